@@ -1,0 +1,121 @@
+/* pt.h — C ABI of libpt.so: the B200 (sm_100a) CUDA path tracer that replaces the reference's
+ * OpenGL dispatch of its per-pixel pathTracing() fragment shaders.
+ *
+ * The reference has no plugin/FFI layer; its "interface" to the hot path is the set of GL calls that
+ * hand buffers and uniforms to pass1.fsh and draw the full-screen quad.  Each entry point below names
+ * the reference call sites it replaces.  Citations: "M:" = ImportanceSampling_LowDiscrepancySequence/
+ * main.cpp, "P:" = ImportanceSampling_LowDiscrepancySequence/shaders/pass1.fsh (OpenglRayTracing/ and
+ * DisneyBRDF/ carry the same host code and the two smaller shaders).
+ *
+ * Conventions: plain C, no torch / C++ types.  Every function returns PT_OK (0) or a negative PT_E*
+ * code; pt_last_error() returns a thread-local message.  Nothing here calls exit() (the reference
+ * does, M:176, M:270) and no exception crosses the boundary.  Host arrays are caller-owned and copied
+ * during the call.  A context is bound to one CUDA device and one stream; calls on one context are not
+ * thread-safe (the reference is single-threaded GLUT); different contexts may be driven from different
+ * threads/processes (one per GPU).  There is no CPU fallback: without a CUDA device pt_create fails.
+ */
+#ifndef PT_H
+#define PT_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PT_OK          0
+#define PT_EINVAL     -1   /* bad argument */
+#define PT_ECUDA      -2   /* a CUDA runtime call failed (message has the CUDA error string) */
+#define PT_ENOSCENE   -3   /* render/readback before pt_upload_scene */
+#define PT_ERANGE     -4   /* index not representable in the reference's float encoding (>= 2^24), M:817-818 */
+#define PT_ENOMEM     -5
+#define PT_EFORMAT    -6   /* malformed node/triangle array (child or leaf range out of bounds) */
+
+/* which fragment shader of the reference the kernels reproduce */
+#define PT_VARIANT_LAMBERT        0   /* OpenglRayTracing/shaders/pass1.fsh   — maxBounce 2 (O:385) */
+#define PT_VARIANT_DISNEY_UNIFORM 1   /* DisneyBRDF/shaders/pass1.fsh         — maxBounce 5 (D:502) */
+#define PT_VARIANT_DISNEY_IS_MIS  2   /* ImportanceSampling_…/shaders/pass1.fsh — maxBounce 2 (P:861) */
+
+/* arithmetic mode */
+#define PT_MODE_FAST          0   /* wide-node culled traversal; CUDA fast math + FMA in shading; exact (IEEE,
+                                     un-fused) ray generation and ray/box/triangle tests */
+#define PT_MODE_PARITY_REF    1   /* reference layout (48 B nodes, 144 B triangles), reference traversal without
+                                     culling, no FMA, include/ptmath.h transcendental functions: bit-identical to
+                                     the CPU oracle */
+#define PT_MODE_PARITY_WIDE   2   /* the fast traversal + data layout under the parity arithmetic: bit-identical
+                                     to the oracle too — proves the traversal restructuring changes no result */
+
+typedef struct PtConfig {
+    int variant;        /* PT_VARIANT_* */
+    int width, height;  /* framebuffer size; pass1.width/height M:82-83, uniforms M:871-872 */
+    int max_bounce;     /* <= 0: the variant's default (2 / 5 / 2); variant 2 supports <= 4 (8 Sobol dims, P:92) */
+    int device;         /* CUDA device ordinal */
+    int mode;           /* PT_MODE_* */
+} PtConfig;
+
+typedef struct PtStats {
+    unsigned long long rays;          /* hitBVH calls (primary + shadow + bounce) since the last reset */
+    unsigned long long samples;       /* pixel-samples rendered since the last reset */
+    double render_ms;                 /* device time of pt_render_spp launches since the last reset (CUDA events) */
+    unsigned long long launches;      /* kernels launched by this context since the last reset */
+    int max_stack_depth;              /* deepest traversal stack the uploaded BVH can need */
+    int n_inner_nodes;                /* wide nodes built at upload */
+    int n_materials;                  /* distinct materials found at upload */
+} PtStats;
+
+typedef struct pt_ctx pt_ctx;
+
+/* glutCreateWindow + getShaderProgram + the three RGBA32F attachments (M:746-751, M:862-866): allocates the
+   fp32 accumulation framebuffer (zeroed) and the context's stream. */
+int pt_create(const PtConfig* cfg, pt_ctx** out);
+int pt_destroy(pt_ctx* ctx);
+
+/* glBufferData + glTexBuffer(GL_RGB32F) x2 (M:825-840) and glTexImage2D x2 + hdrResolution (M:846-853).
+   tris:  nTriangles x 36 floats, Triangle_encoded (M:50-60).
+   nodes: nNodes x 12 floats, BVHNode_encoded (M:68-72); node 0 is the dummy, root is node 1 (M:780-788).
+   hdr:   hdrH x hdrW x 3 floats, rows in file order (sampled NEAREST + CLAMP_TO_EDGE, M:185-195).
+   hdrCache: same shape, calculateHdrCache output (M:555-652); may be NULL for variants 0 and 1.
+   Validates the tree, then repacks on the device into the traversal layout (DESIGN.md "HBM layout"). */
+int pt_upload_scene(pt_ctx* ctx, const float* tris, int nTriangles, const float* nodes, int nNodes,
+                    const float* hdr, const float* hdrCache, int hdrW, int hdrH);
+
+/* glUniform3fv(eye) + glUniformMatrix4fv(cameraRotate, GL_FALSE) (M:678-679): cameraRotate is column-major. */
+int pt_set_camera(pt_ctx* ctx, const float eye[3], const float cameraRotate[16]);
+
+/* Restricts rendering to the pixel rectangle [x0,x1) x [y0,y1) (y = 0 is the bottom row) — the tile split of
+   multi-GPU runs.  Default: the whole image.  (No reference equivalent: glViewport is always full, M:125.) */
+int pt_set_region(pt_ctx* ctx, int x0, int y0, int x1, int y1);
+
+/* pass1.draw() + pass2.draw() for frameCounter = first_frame .. first_frame + n_frames - 1 (M:680, M:704-705):
+   one sample per pixel per frame, running mean mix(last, colour, 1/(frame+1)) (P:868-869) kept in the fp32
+   framebuffer.  Asynchronous on the context's stream. */
+int pt_render_spp(pt_ctx* ctx, unsigned first_frame, unsigned n_frames);
+
+/* Zeroes the framebuffer (frameCounter = 0 after a camera move, M:718, M:737, makes the first mix() discard it). */
+int pt_clear(pt_ctx* ctx);
+
+/* New (the reference never reads pixels back): W*H float4, row 0 = bottom row (GL window origin). Synchronises. */
+int pt_readback(pt_ctx* ctx, float* rgba, size_t bytes);
+/* Parity hook: triangle index (into the uploaded array) of the primary hit of the LAST frame rendered, -1 = miss. */
+int pt_readback_primary_ids(pt_ctx* ctx, int* ids, size_t bytes);
+
+/* Multi-GPU plumbing: the device pointer of the framebuffer (W*H float4) and the context's cudaStream_t, so a
+   host (torch.distributed / NCCL) can reduce or gather in place without a host round trip. */
+int pt_framebuffer_device_ptr(pt_ctx* ctx, void** dptr, size_t* bytes);
+int pt_stream(pt_ctx* ctx, void** cuda_stream);
+/* Multiplies the framebuffer by `scale` and optionally applies pass3.fsh's tone map (pass3.fsh:14-24) into
+   rgba8 (may be NULL) — the epilogue after a sample-split NCCL sum. */
+int pt_scale_framebuffer(pt_ctx* ctx, float scale);
+
+int pt_synchronize(pt_ctx* ctx);
+int pt_get_stats(pt_ctx* ctx, PtStats* out);
+int pt_reset_stats(pt_ctx* ctx);
+
+const char* pt_last_error(void);
+/* "sm_100a" build tag + whether a CUDA device is visible; never fails (used by the CPU-only symbol test) */
+const char* pt_build_info(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PT_H */

@@ -1,0 +1,79 @@
+"""In-tree build of the native libraries (explicit g++/nvcc commands, no JIT cache).
+
+    libptscene.so   host scene library            (g++, csrc/scene/*.cpp)
+    libpt.so        CUDA path tracer, C ABI       (nvcc -gencode arch=compute_100a,code=sm_100a)
+
+The built .so files are git-ignored but travel to the GPU box with the snapshot.  nvcc cross-compiles
+for sm_100a without a GPU.  Two translation units hold the render kernels because they need different
+floating-point contracts: pt_kernels_parity.cu is compiled with -fmad=false (bit-exact against the
+oracle), pt_kernels_fast.cu with FMA contraction.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+ROOT = os.path.dirname(HERE)
+BUILD = os.path.join(HERE, "build")
+
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+NVCC_COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
+SCENE_SRC = ["pts_scene.cpp", "pts_bvh.cpp", "pts_hdr.cpp", "pts_meshgen.cpp"]
+CUDA_HDRS = ["pt_common.cuh", "pt_trace.cuh", "pt_shade.cuh", "pt_sobol_v.inc"]
+
+
+def _run(cmd, log=None):
+    print("+", " ".join(cmd), flush=True)
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if log:
+        with open(log, "w") as f:
+            f.write(r.stdout)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("build step failed: " + " ".join(cmd))
+    return r.stdout
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def build_scene(force=False):
+    srcs = [os.path.join(CSRC, "scene", s) for s in SCENE_SRC]
+    deps = srcs + [os.path.join(CSRC, "scene", h) for h in ("pts_scene.h", "pts_math.h")] + [os.path.join(ROOT, "include", "ptscene.h")]
+    out = os.path.join(HERE, "libptscene.so")
+    if force or _stale(out, deps):
+        _run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared",
+              "-Wall", "-Wextra", *srcs, "-o", out])
+    return out
+
+
+def build_pt(force=False):
+    os.makedirs(BUILD, exist_ok=True)
+    hdrs = [os.path.join(CSRC, h) for h in CUDA_HDRS] + [os.path.join(ROOT, "include", "pt.h"), os.path.join(ROOT, "include", "ptmath.h")]
+    units = [("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", []), ("pt_api", [])]
+    objs = []
+    for name, extra in units:
+        src = os.path.join(CSRC, name + ".cu")
+        obj = os.path.join(BUILD, name + ".o")
+        if force or _stale(obj, [src] + hdrs):
+            _run(["nvcc", *ARCH, *NVCC_COMMON, *extra, "-c", src, "-o", obj], log=os.path.join(BUILD, name + ".ptxas.log"))
+        objs.append(obj)
+    out = os.path.join(HERE, "libpt.so")
+    if force or _stale(out, objs):
+        _run(["nvcc", *ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-o", out])
+    return out
+
+
+def build_all(force=False):
+    return build_scene(force), build_pt(force)
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv)

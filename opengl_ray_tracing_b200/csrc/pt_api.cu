@@ -1,0 +1,504 @@
+// pt_api.cu — the C ABI of libpt.so (include/pt.h) and the upload-time repack kernels.
+//
+// pt_upload_scene keeps a verbatim device copy of the reference-layout buffers (what the reference hands to
+// glBufferData / glTexImage2D, IS/main.cpp:825-853) and derives the traversal layout from it ON THE DEVICE:
+//   wide nodes   64 B / inner node : both child boxes + packed child refs, inner nodes compacted in the
+//                                    reference's (DFS pre-order) numbering so a left child is the next record
+//   trigeo       48 B / triangle   : p1,p2,p3 + the unit face normal, computed with the exact operations of
+//                                    hitTriangle (P:263) so the precomputation changes no bit
+//   trishade     48 B / triangle   : vertex normals + material id (fetched once per ray, for the winning hit)
+//   materials    64 B / material   : de-duplicated (the reference stores all 72 B per triangle)
+//   hdr4/cache4  16 B / texel      : float4 instead of 12-byte texels that straddle sectors
+#include <cub/device/device_scan.cuh>
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/pt.h"
+#include "pt_common.cuh"
+
+namespace pt {
+cudaError_t launch_parity(const RenderParams& p, int variant, bool reference_layout, cudaStream_t stream);
+cudaError_t launch_fast(const RenderParams& p, int variant, cudaStream_t stream);
+}
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(PT_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));             \
+    } while (0)
+
+struct pt_ctx {
+    PtConfig cfg;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // framebuffer
+    float4* accum = nullptr;
+    int* primary_ids = nullptr;
+    unsigned long long* ray_counter = nullptr;
+    int* error_flag = nullptr;
+    // scene
+    bool has_scene = false;
+    float *tris_raw = nullptr, *nodes_raw = nullptr;
+    float4 *wnodes = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr;
+    pt::DevScene sc;
+    // camera + region
+    float eye[3] = {0, 0, 4};
+    float cam[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 4, 1};
+    int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    // stats
+    unsigned long long samples = 0, launches = 0;
+    double render_ms = 0.0;
+    bool timing_pending = false;
+};
+
+// ------------------------------------------------------------------------------------------------
+// upload kernels
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+using namespace pt;
+
+__global__ void k_flag_inner(const float* __restrict__ nodes, int nNodes, int* __restrict__ flag) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nNodes) return;
+    // node 0 is the reference's dummy (IS/main.cpp:780-786); inner <=> n == 0
+    flag[i] = (i >= 1 && (int)nodes[12 * (size_t)i + 3] == 0) ? 1 : 0;
+}
+
+__device__ __forceinline__ uint32_t child_ref(const float* __restrict__ nodes, const int* __restrict__ widx, int c) {
+    const float* nd = nodes + 12 * (size_t)c;
+    int n = (int)nd[3], index = (int)nd[4];
+    return n > 0 ? ref_pack((uint32_t)index, (uint32_t)n) : ref_pack((uint32_t)widx[c], 0u);
+}
+
+__global__ void k_build_wide(const float* __restrict__ nodes, int nNodes, const int* __restrict__ flag,
+                             const int* __restrict__ widx, float4* __restrict__ wnodes) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nNodes || !flag[i]) return;
+    const float* nd = nodes + 12 * (size_t)i;
+    int l = (int)nd[0], r = (int)nd[1];
+    const float* L = nodes + 12 * (size_t)l;
+    const float* R = nodes + 12 * (size_t)r;
+    float4* w = wnodes + 4 * (size_t)widx[i];
+    w[0] = make_float4(L[6], L[7], L[8], L[9]);
+    w[1] = make_float4(L[10], L[11], R[6], R[7]);
+    w[2] = make_float4(R[8], R[9], R[10], R[11]);
+    w[3] = make_float4(__uint_as_float(child_ref(nodes, widx, l)), __uint_as_float(child_ref(nodes, widx, r)), 0.f, 0.f);
+}
+
+__global__ void k_build_tris(const float* __restrict__ tris, int nTriangles, const int* __restrict__ mat_id,
+                             float4* __restrict__ geo, float4* __restrict__ shade) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nTriangles) return;
+    const float* t = tris + 36 * (size_t)i;
+    V3 p1 = mk3(t[0], t[1], t[2]), p2 = mk3(t[3], t[4], t[5]), p3 = mk3(t[6], t[7], t[8]);
+    V3 N = s_normalize(s_cross(s_sub3(p2, p1), s_sub3(p3, p1)));          // hitTriangle, P:263
+    geo[3 * (size_t)i] = make_float4(p1.x, p1.y, p1.z, N.x);
+    geo[3 * (size_t)i + 1] = make_float4(p2.x, p2.y, p2.z, N.y);
+    geo[3 * (size_t)i + 2] = make_float4(p3.x, p3.y, p3.z, N.z);
+    shade[3 * (size_t)i] = make_float4(t[9], t[10], t[11], __int_as_float(mat_id[i]));
+    shade[3 * (size_t)i + 1] = make_float4(t[12], t[13], t[14], 0.f);
+    shade[3 * (size_t)i + 2] = make_float4(t[15], t[16], t[17], 0.f);
+}
+
+__global__ void k_rgb_to_float4(const float* __restrict__ src, size_t n, float4* __restrict__ dst) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    dst[i] = make_float4(src[3 * i], src[3 * i + 1], src[3 * i + 2], 0.f);
+}
+
+__global__ void k_scale(float4* __restrict__ a, size_t n, float s) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = a[i];
+    a[i] = make_float4(v.x * s, v.y * s, v.z * s, v.w);
+}
+
+struct MatKey {
+    float f[18];
+    bool operator==(const MatKey& o) const { return std::memcmp(f, o.f, sizeof f) == 0; }
+};
+struct MatHash {
+    size_t operator()(const MatKey& k) const {
+        uint64_t h = 1469598103934665603ull;
+        const unsigned char* p = reinterpret_cast<const unsigned char*>(k.f);
+        for (size_t i = 0; i < sizeof k.f; i++) { h ^= p[i]; h *= 1099511628211ull; }
+        return (size_t)h;
+    }
+};
+
+void free_scene(pt_ctx* c) {
+    cudaFree(c->tris_raw); cudaFree(c->nodes_raw); cudaFree(c->wnodes); cudaFree(c->trigeo); cudaFree(c->trishade);
+    cudaFree(c->materials); cudaFree(c->hdr4); cudaFree(c->cache4);
+    c->tris_raw = c->nodes_raw = nullptr;
+    c->wnodes = c->trigeo = c->trishade = c->materials = c->hdr4 = c->cache4 = nullptr;
+    c->has_scene = false;
+}
+
+// Host-side validation of the reference-layout tree: every index in range, children after their parent
+// (the builders emit pre-order), both children present on inner nodes.  Returns the tree depth or < 0.
+int validate_tree(const float* nodes, int nNodes, int nTriangles, std::string& why) {
+    if (nNodes < 2) { why = "need the dummy node 0 and a root node 1"; return -1; }
+    std::vector<int> depth((size_t)nNodes, 0);
+    depth[1] = 1;
+    int max_depth = 1;
+    for (int i = 1; i < nNodes; i++) {
+        const float* nd = nodes + 12 * (size_t)i;
+        int l = (int)nd[0], r = (int)nd[1], n = (int)nd[3], index = (int)nd[4];
+        if ((float)l != nd[0] || (float)r != nd[1] || (float)n != nd[3] || (float)index != nd[4]) { why = "non-integer index in node " + std::to_string(i); return -1; }
+        if (n > 0) {
+            if (index < 0 || (long long)index + n > nTriangles) { why = "leaf range out of bounds in node " + std::to_string(i); return -1; }
+            if (n > 255) { why = "leaf with more than 255 triangles (node " + std::to_string(i) + ")"; return -1; }
+        } else {
+            if (l <= i || r <= i || l >= nNodes || r >= nNodes) { why = "child index out of order/bounds in node " + std::to_string(i); return -1; }
+            if (depth[i] == 0) { why = "node " + std::to_string(i) + " is unreachable"; return -1; }
+            depth[l] = depth[r] = depth[i] + 1;
+            if (depth[i] + 1 > max_depth) max_depth = depth[i] + 1;
+        }
+    }
+    return max_depth;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* pt_last_error(void) { return g_err.c_str(); }
+
+const char* pt_build_info(void) {
+    static char buf[160];
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    std::snprintf(buf, sizeof buf, "libpt sm_100a cuda-runtime %d devices=%d%s", CUDART_VERSION, e == cudaSuccess ? n : 0,
+                  e == cudaSuccess ? "" : " (no CUDA device: this library has no CPU fallback)");
+    return buf;
+}
+
+int pt_create(const PtConfig* cfg, pt_ctx** out) {
+    if (!cfg || !out) return fail(PT_EINVAL, "pt_create: null argument");
+    if (cfg->variant < 0 || cfg->variant > 2) return fail(PT_EINVAL, "pt_create: variant must be 0, 1 or 2");
+    if (cfg->mode < 0 || cfg->mode > 2) return fail(PT_EINVAL, "pt_create: mode must be PT_MODE_FAST/PARITY_REF/PARITY_WIDE");
+    if (cfg->width <= 0 || cfg->height <= 0 || cfg->width > 16384 || cfg->height > 16384)
+        return fail(PT_EINVAL, "pt_create: width/height out of range");
+    int mb = cfg->max_bounce > 0 ? cfg->max_bounce : (cfg->variant == PT_VARIANT_DISNEY_UNIFORM ? 5 : 2);
+    if (cfg->variant == PT_VARIANT_DISNEY_IS_MIS && mb > 4)
+        return fail(PT_EINVAL, "pt_create: variant 2 supports max_bounce <= 4 (8 Sobol dimensions, pass1.fsh:92)");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(PT_EINVAL, "pt_create: no such CUDA device");
+    CK(cudaSetDevice(cfg->device));
+    pt_ctx* c = new (std::nothrow) pt_ctx();
+    if (!c) return fail(PT_ENOMEM, "pt_create: out of host memory");
+    c->cfg = *cfg;
+    c->cfg.max_bounce = mb;
+    c->x1 = cfg->width; c->y1 = cfg->height;
+    std::memset(&c->sc, 0, sizeof c->sc);
+    size_t npx = (size_t)cfg->width * cfg->height;
+    cudaError_t e;
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
+        (e = cudaMalloc(&c->accum, npx * sizeof(float4))) != cudaSuccess ||
+        (e = cudaMalloc(&c->primary_ids, npx * sizeof(int))) != cudaSuccess ||
+        (e = cudaMalloc(&c->ray_counter, sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMalloc(&c->error_flag, sizeof(int))) != cudaSuccess ||
+        (e = cudaMemsetAsync(c->error_flag, 0, sizeof(int), c->stream)) != cudaSuccess ||
+        (e = cudaMemsetAsync(c->accum, 0, npx * sizeof(float4), c->stream)) != cudaSuccess ||
+        (e = cudaMemsetAsync(c->primary_ids, 0xff, npx * sizeof(int), c->stream)) != cudaSuccess ||
+        (e = cudaMemsetAsync(c->ray_counter, 0, sizeof(unsigned long long), c->stream)) != cudaSuccess) {
+        pt_destroy(c);
+        return fail(PT_ECUDA, std::string("pt_create: ") + cudaGetErrorString(e));
+    }
+    *out = c;
+    return PT_OK;
+}
+
+int pt_destroy(pt_ctx* c) {
+    if (!c) return PT_OK;
+    cudaSetDevice(c->cfg.device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return PT_OK;
+}
+
+int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* nodes, int nNodes, const float* hdr,
+                    const float* hdrCache, int hdrW, int hdrH) {
+    if (!c || !tris || !nodes || !hdr) return fail(PT_EINVAL, "pt_upload_scene: null argument");
+    if (nTriangles <= 0 || nNodes < 2 || hdrW <= 0 || hdrH <= 0) return fail(PT_EINVAL, "pt_upload_scene: empty scene or HDR map");
+    if (nTriangles >= (1 << 24) || nNodes >= (1 << 24))
+        return fail(PT_ERANGE, "pt_upload_scene: index not exact in the reference's float encoding (>= 2^24)");
+    if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS && !hdrCache)
+        return fail(PT_EINVAL, "pt_upload_scene: variant 2 needs the hdrCache table (calculateHdrCache)");
+    std::string why;
+    int depth = validate_tree(nodes, nNodes, nTriangles, why);
+    if (depth < 0) return fail(PT_EFORMAT, "pt_upload_scene: " + why);
+    // depth > 256 is accepted: the reference's stack[256] (pass1.fsh:340) only overflows if a RAY defers more than
+    // 256 subtrees at once, which the kernels detect at run time (PT_ERANGE at the next synchronising call).
+
+    // material de-duplication (host hash over the 18 material floats of each triangle)
+    std::vector<int> mat_id((size_t)nTriangles);
+    std::vector<float> mat_table;
+    {
+        std::unordered_map<MatKey, int, MatHash> seen;
+        MatKey k, last;
+        int last_id = -1;
+        for (int i = 0; i < nTriangles; i++) {
+            std::memcpy(k.f, tris + 36 * (size_t)i + 18, sizeof k.f);
+            if (last_id >= 0 && k == last) { mat_id[i] = last_id; continue; }
+            auto it = seen.find(k);
+            int id;
+            if (it == seen.end()) {
+                id = (int)seen.size();
+                seen.emplace(k, id);
+                const float* f = k.f;                 // emissive, baseColor, 12 params (IS/main.cpp:806-811)
+                const float rec[16] = {f[0], f[1], f[2], f[6], f[3], f[4], f[5], f[7],
+                                       f[8], f[9], f[10], f[11], f[12], f[13], f[14], f[15]};
+                mat_table.insert(mat_table.end(), rec, rec + 16);
+            } else id = it->second;
+            mat_id[i] = id; last = k; last_id = id;
+        }
+    }
+    const int nMaterials = (int)(mat_table.size() / 16);
+
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    free_scene(c);
+    cudaStream_t st = c->stream;
+    const size_t ntex = (size_t)hdrW * hdrH;
+    int *d_flag = nullptr, *d_widx = nullptr, *d_matid = nullptr;
+    float* d_tmp = nullptr;
+    void* d_scan = nullptr;
+    size_t scan_bytes = 0;
+    int nInner = 0;
+    int rc = PT_OK;
+#define CKU(call)                                                                                  \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) { rc = fail(PT_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); goto done; } \
+    } while (0)
+    CKU(cudaMalloc(&c->tris_raw, (size_t)nTriangles * 36 * sizeof(float)));
+    CKU(cudaMalloc(&c->nodes_raw, (size_t)nNodes * 12 * sizeof(float)));
+    CKU(cudaMemcpyAsync(c->tris_raw, tris, (size_t)nTriangles * 36 * sizeof(float), cudaMemcpyHostToDevice, st));
+    CKU(cudaMemcpyAsync(c->nodes_raw, nodes, (size_t)nNodes * 12 * sizeof(float), cudaMemcpyHostToDevice, st));
+    // wide nodes: flag inner nodes, exclusive scan -> compact index, build
+    CKU(cudaMalloc(&d_flag, (size_t)nNodes * sizeof(int)));
+    CKU(cudaMalloc(&d_widx, (size_t)nNodes * sizeof(int)));
+    k_flag_inner<<<(nNodes + 255) / 256, 256, 0, st>>>(c->nodes_raw, nNodes, d_flag);
+    CKU(cudaGetLastError());
+    CKU(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, d_flag, d_widx, nNodes, st));
+    CKU(cudaMalloc(&d_scan, scan_bytes ? scan_bytes : 1));
+    CKU(cub::DeviceScan::ExclusiveSum(d_scan, scan_bytes, d_flag, d_widx, nNodes, st));
+    {
+        int last_flag = 0, last_idx = 0;
+        CKU(cudaMemcpyAsync(&last_flag, d_flag + (nNodes - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        CKU(cudaMemcpyAsync(&last_idx, d_widx + (nNodes - 1), sizeof(int), cudaMemcpyDeviceToHost, st));
+        CKU(cudaStreamSynchronize(st));
+        nInner = last_idx + last_flag;
+    }
+    CKU(cudaMalloc(&c->wnodes, (size_t)(nInner > 0 ? nInner : 1) * 4 * sizeof(float4)));
+    if (nInner > 0) {
+        k_build_wide<<<(nNodes + 255) / 256, 256, 0, st>>>(c->nodes_raw, nNodes, d_flag, d_widx, c->wnodes);
+        CKU(cudaGetLastError());
+    }
+    // triangles
+    CKU(cudaMalloc(&d_matid, (size_t)nTriangles * sizeof(int)));
+    CKU(cudaMemcpyAsync(d_matid, mat_id.data(), (size_t)nTriangles * sizeof(int), cudaMemcpyHostToDevice, st));
+    CKU(cudaMalloc(&c->trigeo, (size_t)nTriangles * 3 * sizeof(float4)));
+    CKU(cudaMalloc(&c->trishade, (size_t)nTriangles * 3 * sizeof(float4)));
+    k_build_tris<<<(nTriangles + 255) / 256, 256, 0, st>>>(c->tris_raw, nTriangles, d_matid, c->trigeo, c->trishade);
+    CKU(cudaGetLastError());
+    CKU(cudaMalloc(&c->materials, (size_t)nMaterials * 4 * sizeof(float4)));
+    CKU(cudaMemcpyAsync(c->materials, mat_table.data(), (size_t)nMaterials * 16 * sizeof(float), cudaMemcpyHostToDevice, st));
+    // environment
+    CKU(cudaMalloc(&d_tmp, ntex * 3 * sizeof(float)));
+    CKU(cudaMalloc(&c->hdr4, ntex * sizeof(float4)));
+    CKU(cudaMemcpyAsync(d_tmp, hdr, ntex * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+    k_rgb_to_float4<<<(unsigned)((ntex + 255) / 256), 256, 0, st>>>(d_tmp, ntex, c->hdr4);
+    CKU(cudaGetLastError());
+    if (hdrCache) {
+        CKU(cudaMalloc(&c->cache4, ntex * sizeof(float4)));
+        CKU(cudaStreamSynchronize(st));
+        CKU(cudaMemcpyAsync(d_tmp, hdrCache, ntex * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+        k_rgb_to_float4<<<(unsigned)((ntex + 255) / 256), 256, 0, st>>>(d_tmp, ntex, c->cache4);
+        CKU(cudaGetLastError());
+    }
+    CKU(cudaStreamSynchronize(st));
+    {
+        pt::DevScene& s = c->sc;
+        s.tris_raw = c->tris_raw; s.nodes_raw = c->nodes_raw; s.wnodes = c->wnodes; s.trigeo = c->trigeo;
+        s.trishade = c->trishade; s.materials = c->materials; s.hdr4 = c->hdr4; s.cache4 = c->cache4;
+        s.nTriangles = nTriangles; s.nNodes = nNodes; s.nInner = nInner; s.nMaterials = nMaterials;
+        s.hdrW = hdrW; s.hdrH = hdrH; s.stack_depth = depth; s.error_flag = c->error_flag;
+        // root = node 1: a leaf when the whole scene fits one leaf, else wide node 0
+        int rn = (int)nodes[12 + 3], rindex = (int)nodes[12 + 4];
+        s.root_ref = rn > 0 ? pt::ref_pack((uint32_t)rindex, (uint32_t)rn) : pt::ref_pack(0u, 0u);
+        c->has_scene = true;
+        c->launches += 4 + (hdrCache ? 1 : 0);
+    }
+done:
+    cudaFree(d_flag); cudaFree(d_widx); cudaFree(d_matid); cudaFree(d_tmp); cudaFree(d_scan);
+    if (rc != PT_OK) free_scene(c);
+    return rc;
+#undef CKU
+}
+
+int pt_set_camera(pt_ctx* c, const float eye[3], const float cam[16]) {
+    if (!c || !eye || !cam) return fail(PT_EINVAL, "pt_set_camera: null argument");
+    std::memcpy(c->eye, eye, 12);
+    std::memcpy(c->cam, cam, 64);
+    return PT_OK;
+}
+
+int pt_set_region(pt_ctx* c, int x0, int y0, int x1, int y1) {
+    if (!c) return fail(PT_EINVAL, "pt_set_region: null context");
+    if (x0 < 0 || y0 < 0 || x1 > c->cfg.width || y1 > c->cfg.height || x0 >= x1 || y0 >= y1)
+        return fail(PT_EINVAL, "pt_set_region: rectangle outside the framebuffer or empty");
+    c->x0 = x0; c->y0 = y0; c->x1 = x1; c->y1 = y1;
+    return PT_OK;
+}
+
+static int collect_timing(pt_ctx* c) {
+    if (!c->timing_pending) return PT_OK;
+    float ms = 0.f;
+    CK(cudaEventSynchronize(c->ev1));
+    CK(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->render_ms += ms;
+    c->timing_pending = false;
+    int flag = 0;
+    CK(cudaMemcpy(&flag, c->error_flag, sizeof flag, cudaMemcpyDeviceToHost));
+    if (flag) {
+        CK(cudaMemset(c->error_flag, 0, sizeof flag));
+        return fail(PT_ERANGE, "render kernel: traversal stack overflow (a ray deferred more than 256 subtrees; "
+                               "the reference's own stack[256], pass1.fsh:340, would have been overrun) - image is invalid");
+    }
+    return PT_OK;
+}
+
+int pt_render_spp(pt_ctx* c, unsigned first_frame, unsigned n_frames) {
+    if (!c) return fail(PT_EINVAL, "pt_render_spp: null context");
+    if (!c->has_scene) return fail(PT_ENOSCENE, "pt_render_spp: no scene uploaded");
+    if (n_frames == 0) return PT_OK;
+    CK(cudaSetDevice(c->cfg.device));
+    int rc = collect_timing(c);
+    if (rc != PT_OK) return rc;
+    pt::RenderParams p;
+    p.sc = c->sc;
+    std::memcpy(p.eye, c->eye, 12);
+    std::memcpy(p.cam, c->cam, 64);
+    p.width = c->cfg.width; p.height = c->cfg.height;
+    p.x0 = c->x0; p.y0 = c->y0; p.x1 = c->x1; p.y1 = c->y1;
+    p.first_frame = first_frame; p.n_frames = n_frames;
+    p.max_bounce = c->cfg.max_bounce;
+    p.accum = c->accum; p.primary_ids = c->primary_ids; p.ray_counter = c->ray_counter;
+    CK(cudaEventRecord(c->ev0, c->stream));
+    cudaError_t e = c->cfg.mode == PT_MODE_FAST ? pt::launch_fast(p, c->cfg.variant, c->stream)
+                                                 : pt::launch_parity(p, c->cfg.variant, c->cfg.mode == PT_MODE_PARITY_REF, c->stream);
+    if (e != cudaSuccess) return fail(PT_ECUDA, std::string("render kernel launch: ") + cudaGetErrorString(e));
+    CK(cudaEventRecord(c->ev1, c->stream));
+    c->timing_pending = true;
+    c->launches += 1;
+    c->samples += (unsigned long long)(c->x1 - c->x0) * (c->y1 - c->y0) * n_frames;
+    return PT_OK;
+}
+
+int pt_clear(pt_ctx* c) {
+    if (!c) return fail(PT_EINVAL, "pt_clear: null context");
+    CK(cudaSetDevice(c->cfg.device));
+    size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    CK(cudaMemsetAsync(c->accum, 0, npx * sizeof(float4), c->stream));
+    CK(cudaMemsetAsync(c->primary_ids, 0xff, npx * sizeof(int), c->stream));
+    return PT_OK;
+}
+
+int pt_readback(pt_ctx* c, float* rgba, size_t bytes) {
+    if (!c || !rgba) return fail(PT_EINVAL, "pt_readback: null argument");
+    size_t need = (size_t)c->cfg.width * c->cfg.height * sizeof(float4);
+    if (bytes < need) return fail(PT_EINVAL, "pt_readback: buffer too small");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(rgba, c->accum, need, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return collect_timing(c);
+}
+
+int pt_readback_primary_ids(pt_ctx* c, int* ids, size_t bytes) {
+    if (!c || !ids) return fail(PT_EINVAL, "pt_readback_primary_ids: null argument");
+    size_t need = (size_t)c->cfg.width * c->cfg.height * sizeof(int);
+    if (bytes < need) return fail(PT_EINVAL, "pt_readback_primary_ids: buffer too small");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(ids, c->primary_ids, need, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return collect_timing(c);
+}
+
+int pt_framebuffer_device_ptr(pt_ctx* c, void** dptr, size_t* bytes) {
+    if (!c || !dptr) return fail(PT_EINVAL, "pt_framebuffer_device_ptr: null argument");
+    *dptr = c->accum;
+    if (bytes) *bytes = (size_t)c->cfg.width * c->cfg.height * sizeof(float4);
+    return PT_OK;
+}
+
+int pt_stream(pt_ctx* c, void** s) {
+    if (!c || !s) return fail(PT_EINVAL, "pt_stream: null argument");
+    *s = (void*)c->stream;
+    return PT_OK;
+}
+
+int pt_scale_framebuffer(pt_ctx* c, float scale) {
+    if (!c) return fail(PT_EINVAL, "pt_scale_framebuffer: null context");
+    CK(cudaSetDevice(c->cfg.device));
+    size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    k_scale<<<(unsigned)((npx + 255) / 256), 256, 0, c->stream>>>(c->accum, npx, scale);
+    CK(cudaGetLastError());
+    c->launches += 1;
+    return PT_OK;
+}
+
+int pt_synchronize(pt_ctx* c) {
+    if (!c) return fail(PT_EINVAL, "pt_synchronize: null context");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    return collect_timing(c);
+}
+
+int pt_get_stats(pt_ctx* c, PtStats* out) {
+    if (!c || !out) return fail(PT_EINVAL, "pt_get_stats: null argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    int rc = collect_timing(c);
+    if (rc != PT_OK) return rc;
+    unsigned long long rays = 0;
+    CK(cudaMemcpy(&rays, c->ray_counter, sizeof rays, cudaMemcpyDeviceToHost));
+    out->rays = rays; out->samples = c->samples; out->render_ms = c->render_ms; out->launches = c->launches;
+    out->max_stack_depth = c->has_scene ? c->sc.stack_depth : 0;
+    out->n_inner_nodes = c->has_scene ? c->sc.nInner : 0;
+    out->n_materials = c->has_scene ? c->sc.nMaterials : 0;
+    return PT_OK;
+}
+
+int pt_reset_stats(pt_ctx* c) {
+    if (!c) return fail(PT_EINVAL, "pt_reset_stats: null context");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    int rc = collect_timing(c);
+    if (rc != PT_OK) return rc;
+    CK(cudaMemset(c->ray_counter, 0, sizeof(unsigned long long)));
+    c->samples = 0; c->launches = 0; c->render_ms = 0.0;
+    return PT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,123 @@
+// pt_common.cuh — device-side types shared by the upload, traversal and shading code of libpt.so.
+//
+// Arithmetic discipline (DESIGN.md "Arithmetic modes"):
+//   * "strict" helpers (s_add, s_mul, …) map to the CUDA _rn intrinsics, which are IEEE-754 binary32,
+//     never fused into FMAs and unaffected by fast-math flags.  Ray generation and every ray/box and
+//     ray/triangle test use them in ALL modes: that is what makes primary-hit triangle ids bit-exact.
+//   * plain operators are used in shading.  The parity translation unit is compiled with -fmad=false,
+//     so there they are exactly the oracle's operations; the fast translation unit lets nvcc fuse them.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pt {
+
+struct V3 {
+    float x, y, z;
+};
+__device__ __forceinline__ V3 mk3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ V3 operator-(V3 a) { return mk3(-a.x, -a.y, -a.z); }
+// the oracle's definitions of the GLSL built-ins (oracle/glsl_compat.h): same association order
+__device__ __forceinline__ float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+    return mk3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
+}
+__device__ __forceinline__ V3 normalize(V3 v) { return v * (1.0f / sqrtf(dot(v, v))); }
+__device__ __forceinline__ float mixf(float x, float y, float a) { return x * (1.0f - a) + y * a; }
+__device__ __forceinline__ V3 mix3(V3 x, V3 y, float a) { return x * (1.0f - a) + y * a; }
+__device__ __forceinline__ float sqr(float x) { return x * x; }
+
+// ---- strict (never fused, IEEE) arithmetic ------------------------------------------------------
+__device__ __forceinline__ float s_add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float s_sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float s_mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float s_div(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float s_sqrt(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ V3 s_sub3(V3 a, V3 b) { return mk3(s_sub(a.x, b.x), s_sub(a.y, b.y), s_sub(a.z, b.z)); }
+__device__ __forceinline__ float s_dot(V3 a, V3 b) {
+    return s_add(s_add(s_mul(a.x, b.x), s_mul(a.y, b.y)), s_mul(a.z, b.z));
+}
+__device__ __forceinline__ V3 s_cross(V3 a, V3 b) {
+    return mk3(s_sub(s_mul(a.y, b.z), s_mul(b.y, a.z)), s_sub(s_mul(a.z, b.x), s_mul(b.z, a.x)),
+               s_sub(s_mul(a.x, b.y), s_mul(b.x, a.y)));
+}
+__device__ __forceinline__ V3 s_normalize(V3 v) {
+    float k = s_div(1.0f, s_sqrt(s_dot(v, v)));
+    return mk3(s_mul(v.x, k), s_mul(v.y, k), s_mul(v.z, k));
+}
+// S + d*t
+__device__ __forceinline__ V3 s_point(V3 S, V3 d, float t) {
+    return mk3(s_add(S.x, s_mul(d.x, t)), s_add(S.y, s_mul(d.y, t)), s_add(S.z, s_mul(d.z, t)));
+}
+
+// ---- read-only loads: ld.global.nc (the scene is immutable while a render kernel runs) ----------
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+__device__ __forceinline__ float ldg1(const float* p) { return __ldg(p); }
+
+// ---- packed child reference of the wide BVH ----------------------------------------------------
+// bits 0..23 = index (inner: wide-node index; leaf: first triangle), bits 24..31 = triangle count
+// (0 => inner node).  Lossless: the reference's own float encoding caps every index below 2^24.
+#define PT_REF_NONE 0xffffffffu
+__host__ __device__ __forceinline__ uint32_t ref_pack(uint32_t index, uint32_t count) { return (count << 24) | index; }
+__host__ __device__ __forceinline__ uint32_t ref_index(uint32_t r) { return r & 0x00ffffffu; }
+__host__ __device__ __forceinline__ uint32_t ref_count(uint32_t r) { return r >> 24; }
+
+// Everything a render kernel reads.  Passed by value in kernel parameter space.
+struct DevScene {
+    // reference layout, exactly as uploaded (PT_MODE_PARITY_REF traverses these)
+    const float* tris_raw;      // nTriangles x 36 floats  (Triangle_encoded)
+    const float* nodes_raw;     // nNodes x 12 floats      (BVHNode_encoded)
+    // traversal layout built on the device at upload
+    const float4* wnodes;       // nInner x 4 float4 (64 B): child boxes + packed child refs
+    const float4* trigeo;       // nTriangles x 3 float4 (48 B): (p1,N.x) (p2,N.y) (p3,N.z), N = unit face normal
+    const float4* trishade;     // nTriangles x 3 float4 (48 B): (n1, matId) (n2, -) (n3, -)
+    const float4* materials;    // nMaterials x 4 float4 (64 B)
+    const float4* hdr4;         // hdrH x hdrW float4 (rgb, 0)
+    const float4* cache4;       // hdrH x hdrW float4 (x/w, y/h, pdf, 0) or null
+    int nTriangles, nNodes, nInner, nMaterials;
+    int hdrW, hdrH;
+    uint32_t root_ref;
+    int stack_depth;            // depth of the tree = worst-case traversal stack
+    int* error_flag;            // set to PT_ERR_* by a kernel that had to give up (checked at the next sync)
+};
+#define PT_ERR_STACK 1          // traversal stack overflow (> 256 deferred subtrees; the reference's stack[256], P:340)
+
+struct RenderParams {
+    DevScene sc;
+    float eye[3];
+    float cam[16];              // column-major cameraRotate
+    int width, height;
+    int x0, y0, x1, y1;         // region
+    unsigned first_frame, n_frames;
+    int max_bounce;
+    float4* accum;              // W*H float4, row 0 = bottom
+    int* primary_ids;           // W*H
+    unsigned long long* ray_counter;
+};
+
+struct Material {               // P:41-56 without the two fields no shader reads (IOR, transmission)
+    V3 emissive, baseColor;
+    float subsurface, metallic, specular, specularTint, roughness, anisotropic;
+    float sheen, sheenTint, clearcoat, clearcoatGloss;
+};
+
+struct Hit {                    // P:63-71
+    bool isHit, isInside;
+    float distance;
+    V3 hitPoint, normal, viewDir;
+    int tri;
+};
+
+// NEAREST + CLAMP_TO_EDGE texel index (M:190-193): floor(u*n) clamped to [0, n-1]; NaN -> 0
+__device__ __forceinline__ int nearest_texel(float u, int n) {
+    float f = floorf(s_mul(u, (float)n));
+    f = fminf(fmaxf(f, 0.0f), (float)(n - 1));
+    return (int)f;
+}
+
+}  // namespace pt

@@ -1,0 +1,445 @@
+// pt_shade.cuh — per-sample shading: RNG, Sobol, Disney BRDF, HDR environment sampling, MIS, and the
+// render kernel.  One source, three arithmetic configurations (pt_kernels_parity.cu / pt_kernels_fast.cu).
+//
+// Reference functions, by line ("P:" = ImportanceSampling_LowDiscrepancySequence/shaders/pass1.fsh,
+// "D:" = DisneyBRDF/shaders/pass1.fsh, "O:" = OpenglRayTracing/shaders/pass1.fsh):
+//   seed/wang_hash/rand P:73-89 · sobol/grayCode/sobolVec2 P:96-116 · CranleyPattersonRotation P:118-136
+//   SampleHemisphere O:89-95 · toNormalHemisphere P:153-159 · getTangent P:161-172
+//   SampleSphericalMap/sampleHdr P:175-189 · BRDF terms P:386-421 · BRDF_Evaluate_aniso P:423-482
+//   SampleCosineHemisphere/SampleGTR2/SampleGTR1/SampleBRDF P:485-570 · SampleHdr P:573-585
+//   BRDF_Evaluate P:587-636 · hdrColor/hdrPdf P:647-666 · BRDF_Pdf P:669-706 · misMixWeight P:708-711
+//   pathTracing O:329-364, D:443-481 · pathTracingImportanceSampling P:761-841 · main P:844-871
+//
+// Structure: the three shaders call hitBVH from up to three places; here every closest-hit query of a
+// path (primary and bounce rays) goes through ONE traversal site inside a loop, and shadow rays through a
+// second, any-hit site.  What must survive a traversal is kept small: f_r, N·L, pdf, history, Lo.
+#pragma once
+#include "pt_trace.cuh"
+#include "../../include/ptmath.h"
+
+namespace pt {
+
+#define PT_PI 3.1415926f          // P:23 — the shader's own constant, not pi
+
+static __constant__ uint32_t c_sobol_v[8 * 32] = {
+#include "pt_sobol_v.inc"
+};
+
+// ---- arithmetic configurations ------------------------------------------------------------------
+struct MathExact {                // include/ptmath.h: the oracle's definition of the GLSL transcendentals
+    static __device__ __forceinline__ float sin(float a) { return pt_sinf(a); }
+    static __device__ __forceinline__ float cos(float a) { return pt_cosf(a); }
+    static __device__ __forceinline__ float asin(float a) { return pt_asinf(a); }
+    static __device__ __forceinline__ float atan2(float y, float x) { return pt_atan2f(y, x); }
+    static __device__ __forceinline__ float log(float a) { return pt_logf(a); }
+    static __device__ __forceinline__ float pow(float a, float b) { return pt_powf(a, b); }
+};
+struct MathFast {                 // SFU approximations where CUDA has them
+    static __device__ __forceinline__ float sin(float a) { return __sinf(a); }
+    static __device__ __forceinline__ float cos(float a) { return __cosf(a); }
+    static __device__ __forceinline__ float asin(float a) { return asinf(a); }
+    static __device__ __forceinline__ float atan2(float y, float x) { return atan2f(y, x); }
+    static __device__ __forceinline__ float log(float a) { return __logf(a); }
+    static __device__ __forceinline__ float pow(float a, float b) { return __powf(a, b); }
+};
+struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  };
+struct CfgParityWide { typedef MathExact M; static const bool RAW = false; };
+struct CfgFast       { typedef MathFast  M; static const bool RAW = false; };
+
+template <class Cfg, bool ANYHIT>
+__device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d) {
+    if (Cfg::RAW) return trace_ref(sc, o, d);
+    else return trace_wide<ANYHIT, PT_STACK>(sc, o, d);
+}
+
+// ---- RNG and QMC -----------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t wang_hash(uint32_t& seed) {
+    seed = (seed ^ 61u) ^ (seed >> 16);
+    seed *= 9u;
+    seed = seed ^ (seed >> 4);
+    seed *= 0x27d4eb2du;
+    seed = seed ^ (seed >> 15);
+    return seed;
+}
+__device__ __forceinline__ float u2f(uint32_t h) { return s_mul(__uint2float_rn(h), 2.3283064365386963e-10f); }  // /2^32, exact
+__device__ __forceinline__ float rnd(uint32_t& seed) { return u2f(wang_hash(seed)); }
+
+__device__ __forceinline__ float sobol(uint32_t d, uint32_t i) {
+    uint32_t result = 0, offset = d * 32;
+    for (uint32_t j = 0; i != 0; i >>= 1, j++)
+        if (i & 1u) result ^= c_sobol_v[j + offset];
+    return s_mul(__uint2float_rn(result), 2.3283064365386963e-10f);          // 1.0f/float(0xFFFFFFFFU) == 2^-32
+}
+__device__ __forceinline__ void cranley_patterson(int px, int py, float& u, float& v) {
+    uint32_t pseed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + (uint32_t)(114514 / 1919) * 26699u) | 1u;
+    float a = rnd(pseed), b = rnd(pseed);
+    u = s_add(u, a);
+    if (u > 1.0f) u = s_sub(u, 1.0f);
+    if (u < 0.0f) u = s_add(u, 1.0f);
+    v = s_add(v, b);
+    if (v > 1.0f) v = s_sub(v, 1.0f);
+    if (v < 0.0f) v = s_add(v, 1.0f);
+}
+
+// ---- frames ---------------------------------------------------------------------------------------
+__device__ __forceinline__ V3 toNormalHemisphere(V3 v, V3 N) {
+    V3 helper = mk3(1, 0, 0);
+    if (fabsf(N.x) > 0.999f) helper = mk3(0, 0, 1);
+    V3 tangent = normalize(cross(N, helper));
+    V3 bitangent = normalize(cross(N, tangent));
+    return tangent * v.x + bitangent * v.y + N * v.z;
+}
+__device__ __forceinline__ void getTangent(V3 N, V3& tangent, V3& bitangent) {
+    V3 helper = mk3(1, 0, 0);
+    if (fabsf(N.x) > 0.999f) helper = mk3(0, 0, 1);
+    bitangent = normalize(cross(N, helper));
+    tangent = normalize(cross(N, bitangent));
+}
+
+// ---- environment map ----------------------------------------------------------------------------------
+// Direction <-> texel mapping, evaluated in the oracle's arithmetic (strict ops + include/ptmath.h) in EVERY
+// mode.  Reason: calculateHdrCache stores texel CORNERS (x/W, y/H; IS/main.cpp:632-633), so the direction
+// SampleHdr builds from a cache entry maps back to a uv that sits exactly on a texel boundary; which of the
+// two neighbouring texels hdrColor()/hdrPdf() then read (P:647-666) is decided by the last bits of
+// cos/sin/atan/asin.  Leaving those to the SFU approximations flips about half of all light-sample lookups.
+__device__ __forceinline__ void spherical_uv(V3 v, float& u, float& w) {      // SampleSphericalMap, P:175-181
+    V3 n = s_normalize(v);
+    u = s_div(pt_atan2f(n.z, n.x), s_mul(2.0f, PT_PI));
+    w = s_div(pt_asinf(n.y), PT_PI);
+    u = s_add(u, 0.5f);
+    w = s_sub(1.0f, s_add(w, 0.5f));
+}
+__device__ __forceinline__ float4 tex_nearest(const float4* img, int w, int h, float u, float v) {
+    return ldg4(img + (size_t)nearest_texel(v, h) * w + nearest_texel(u, w));
+}
+template <class M> __device__ __forceinline__ V3 sampleHdr(const DevScene& sc, V3 v) {      // clamped to 10, P:184-189
+    float u, w;
+    spherical_uv(v, u, w);
+    float4 c = tex_nearest(sc.hdr4, sc.hdrW, sc.hdrH, u, w);
+    return mk3(fminf(c.x, 10.0f), fminf(c.y, 10.0f), fminf(c.z, 10.0f));
+}
+// hdrColor (unclamped, P:647-651) and hdrPdf (P:655-666) look up the same uv: one atan2/asin for both
+template <class M> __device__ __forceinline__ void hdr_color_pdf(const DevScene& sc, V3 L, V3& color, float& pdf_light) {
+    float u, w;
+    spherical_uv(L, u, w);
+    float4 c = tex_nearest(sc.hdr4, sc.hdrW, sc.hdrH, u, w);
+    color = mk3(c.x, c.y, c.z);
+    float pdf = tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, u, w).z;
+    float theta = PT_PI * (0.5f - w);
+    float sin_theta = fmaxf(M::sin(theta), 1e-10f);
+    float p_convert = (float)(sc.hdrW * sc.hdrW / 2) / (2.0f * PT_PI * PT_PI * sin_theta);
+    pdf_light = pdf * p_convert;
+}
+template <class M> __device__ __forceinline__ V3 SampleHdr(const DevScene& sc, float xi_1, float xi_2) {   // P:573-585
+    float4 c = tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, xi_1, xi_2);
+    float x = c.x, y = s_sub(1.0f, c.y);
+    float phi = s_mul(s_mul(2.0f, PT_PI), s_sub(x, 0.5f));
+    float theta = s_mul(PT_PI, s_sub(y, 0.5f));
+    float ct = pt_cosf(theta);
+    return mk3(s_mul(ct, pt_cosf(phi)), pt_sinf(theta), s_mul(ct, pt_sinf(phi)));
+}
+
+// ---- Disney terms -------------------------------------------------------------------------------------
+__device__ __forceinline__ float SchlickFresnel(float u) {
+    float m = fminf(fmaxf(1.0f - u, 0.0f), 1.0f);
+    float m2 = m * m;
+    return m2 * m2 * m;
+}
+template <class M> __device__ __forceinline__ float GTR1(float NdotH, float a) {
+    if (a >= 1.0f) return 1.0f / PT_PI;
+    float a2 = a * a;
+    float t = 1.0f + (a2 - 1.0f) * NdotH * NdotH;
+    return (a2 - 1.0f) / (PT_PI * M::log(a2) * t);
+}
+__device__ __forceinline__ float GTR2(float NdotH, float a) {
+    float a2 = a * a;
+    float t = 1.0f + (a2 - 1.0f) * NdotH * NdotH;
+    return a2 / (PT_PI * t * t);
+}
+__device__ __forceinline__ float GTR2_aniso(float NdotH, float HdotX, float HdotY, float ax, float ay) {
+    return 1.0f / (PT_PI * ax * ay * sqr(sqr(HdotX / ax) + sqr(HdotY / ay) + NdotH * NdotH));
+}
+__device__ __forceinline__ float smithG_GGX(float NdotV, float alphaG) {
+    float a = alphaG * alphaG, b = NdotV * NdotV;
+    return 1.0f / (NdotV + sqrtf(a + b - a * b));
+}
+__device__ __forceinline__ float smithG_GGX_aniso(float NdotV, float VdotX, float VdotY, float ax, float ay) {
+    return 1.0f / (NdotV + sqrtf(sqr(VdotX * ax) + sqr(VdotY * ay) + sqr(NdotV)));
+}
+
+// Terms shared by both evaluate functions (P:432-448 == P:597-613)
+struct DisneyCommon {
+    V3 Cdlin, Cspec0, Csheen;
+    float Fd, ss, FH, NdotH, LdotH;
+};
+__device__ __forceinline__ DisneyCommon disney_common(V3 V, V3 N, V3 L, float NdotL, float NdotV, const Material& mt) {
+    DisneyCommon c;
+    V3 H = normalize(L + V);
+    c.NdotH = dot(N, H);
+    c.LdotH = dot(L, H);
+    c.Cdlin = mt.baseColor;
+    float Cdlum = 0.3f * c.Cdlin.x + 0.6f * c.Cdlin.y + 0.1f * c.Cdlin.z;
+    V3 Ctint = (Cdlum > 0.0f) ? (c.Cdlin / Cdlum) : mk3(1, 1, 1);
+    V3 Cspec = mix3(mk3(1, 1, 1), Ctint, mt.specularTint) * mt.specular;
+    c.Cspec0 = mix3(Cspec * 0.08f, c.Cdlin, mt.metallic);
+    c.Csheen = mix3(mk3(1, 1, 1), Ctint, mt.sheenTint);
+    float Fd90 = 0.5f + 2.0f * c.LdotH * c.LdotH * mt.roughness;
+    float FL = SchlickFresnel(NdotL), FV = SchlickFresnel(NdotV);
+    c.Fd = mixf(1.0f, Fd90, FL) * mixf(1.0f, Fd90, FV);
+    float Fss90 = c.LdotH * c.LdotH * mt.roughness;
+    float Fss = mixf(1.0f, Fss90, FL) * mixf(1.0f, Fss90, FV);
+    c.ss = 1.25f * (Fss * (1.0f / (NdotL + NdotV) - 0.5f) + 0.5f);
+    c.FH = SchlickFresnel(c.LdotH);
+    return c;
+}
+template <class M>
+__device__ __forceinline__ V3 disney_combine(const DisneyCommon& c, float Gs, float Ds, float NdotL, float NdotV,
+                                             const Material& mt) {
+    V3 Fs = mix3(c.Cspec0, mk3(1, 1, 1), c.FH);
+    V3 specular = (Fs * Gs) * Ds;
+    float Dr = GTR1<M>(c.NdotH, mixf(0.1f, 0.001f, mt.clearcoatGloss));
+    float Fr = mixf(0.04f, 1.0f, c.FH);
+    float Gr = smithG_GGX(NdotL, 0.25f) * smithG_GGX(NdotV, 0.25f);
+    float cc = 0.25f * Gr * Fr * Dr * mt.clearcoat;
+    V3 Fsheen = c.Csheen * (c.FH * mt.sheen);
+    V3 diffuse = c.Cdlin * ((1.0f / PT_PI) * mixf(c.Fd, c.ss, mt.subsurface)) + Fsheen;
+    return diffuse * (1.0f - mt.metallic) + specular + mk3(cc, cc, cc);
+}
+
+// BRDF_Evaluate_aniso P:423-482 (the Disney variant's BRDF_Evaluate, D:381-440)
+template <class M>
+__device__ __forceinline__ V3 BRDF_Evaluate_aniso(V3 V, V3 N, V3 L, V3 X, V3 Y, const Material& mt) {
+    float NdotL = dot(N, L), NdotV = dot(N, V);
+    if (NdotL < 0.0f || NdotV < 0.0f) return mk3(0, 0, 0);
+    DisneyCommon c = disney_common(V, N, L, NdotL, NdotV, mt);
+    V3 H = normalize(L + V);
+    float aspect = sqrtf(1.0f - mt.anisotropic * 0.9f);
+    float ax = fmaxf(0.001f, sqr(mt.roughness) / aspect);
+    float ay = fmaxf(0.001f, sqr(mt.roughness) * aspect);
+    float Ds = GTR2_aniso(c.NdotH, dot(H, X), dot(H, Y), ax, ay);
+    float Gs = smithG_GGX_aniso(NdotL, dot(L, X), dot(L, Y), ax, ay);
+    Gs *= smithG_GGX_aniso(NdotV, dot(V, X), dot(V, Y), ax, ay);
+    return disney_combine<M>(c, Gs, Ds, NdotL, NdotV, mt);
+}
+// isotropic BRDF_Evaluate of the IS shader, P:587-636 (smithG_GGX takes roughness, not alpha: P:620-621)
+template <class M>
+__device__ __forceinline__ V3 BRDF_Evaluate_iso(V3 V, V3 N, V3 L, const Material& mt) {
+    float NdotL = dot(N, L), NdotV = dot(N, V);
+    if (NdotL < 0.0f || NdotV < 0.0f) return mk3(0, 0, 0);
+    DisneyCommon c = disney_common(V, N, L, NdotL, NdotV, mt);
+    float alpha = fmaxf(0.001f, sqr(mt.roughness));
+    float Ds = GTR2(c.NdotH, alpha);
+    float Gs = smithG_GGX(NdotL, mt.roughness);
+    Gs *= smithG_GGX(NdotV, mt.roughness);
+    return disney_combine<M>(c, Gs, Ds, NdotL, NdotV, mt);
+}
+
+// BRDF_Pdf, P:669-706
+template <class M> __device__ __forceinline__ float BRDF_Pdf(V3 V, V3 N, V3 L, const Material& mt) {
+    float NdotL = dot(N, L), NdotV = dot(N, V);
+    if (NdotL < 0.0f || NdotV < 0.0f) return 0.0f;
+    V3 H = normalize(L + V);
+    float NdotH = dot(N, H), LdotH = dot(L, H);
+    float alpha = fmaxf(0.001f, sqr(mt.roughness));
+    float Ds = GTR2(NdotH, alpha);
+    float Dr = GTR1<M>(NdotH, mixf(0.1f, 0.001f, mt.clearcoatGloss));
+    float pdf_diffuse = NdotL / PT_PI;
+    float pdf_specular = Ds * NdotH / (4.0f * LdotH);
+    float pdf_clearcoat = Dr * NdotH / (4.0f * LdotH);
+    float r_diffuse = (1.0f - mt.metallic), r_specular = 1.0f, r_clearcoat = 0.25f * mt.clearcoat;
+    float r_sum = r_diffuse + r_specular + r_clearcoat;
+    float p_diffuse = r_diffuse / r_sum, p_specular = r_specular / r_sum, p_clearcoat = r_clearcoat / r_sum;
+    float pdf = p_diffuse * pdf_diffuse + p_specular * pdf_specular + p_clearcoat * pdf_clearcoat;
+    return fmaxf(1e-10f, pdf);
+}
+__device__ __forceinline__ float misMixWeight(float a, float b) { float t = a * a; return t / (b * b + t); }
+
+// SampleBRDF, P:539-570 with its three lobe samplers P:485-536
+__device__ __forceinline__ V3 reflect3(V3 I, V3 N) { return I - N * (2.0f * dot(N, I)); }
+template <class M>
+__device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 V, V3 N, const Material& mt) {
+    float alpha_GTR1 = mixf(0.1f, 0.001f, mt.clearcoatGloss);
+    float alpha_GTR2 = fmaxf(0.001f, sqr(mt.roughness));
+    float r_diffuse = (1.0f - mt.metallic), r_specular = 1.0f, r_clearcoat = 0.25f * mt.clearcoat;
+    float r_sum = r_diffuse + r_specular + r_clearcoat;
+    float p_diffuse = r_diffuse / r_sum, p_specular = r_specular / r_sum;
+    float rd = xi_3;
+    if (rd <= p_diffuse) {                                        // SampleCosineHemisphere
+        float r = sqrtf(xi_1);
+        float theta = xi_2 * 2.0f * PT_PI;
+        float x = r * M::cos(theta), y = r * M::sin(theta);
+        float z = sqrtf(1.0f - x * x - y * y);
+        return toNormalHemisphere(mk3(x, y, z), N);
+    }
+    float cos_theta_h;
+    if (p_diffuse < rd && rd <= p_diffuse + p_specular) {         // SampleGTR2
+        float alpha = alpha_GTR2;
+        cos_theta_h = sqrtf((1.0f - xi_2) / (1.0f + (alpha * alpha - 1.0f) * xi_2));
+    } else if (p_diffuse + p_specular < rd) {                     // SampleGTR1
+        float alpha = alpha_GTR1;
+        cos_theta_h = sqrtf((1.0f - M::pow(alpha * alpha, 1.0f - xi_2)) / (1.0f - alpha * alpha));
+    } else {
+        return mk3(0, 1, 0);                                      // only reachable through NaNs
+    }
+    float phi_h = 2.0f * PT_PI * xi_1;
+    float sin_phi_h = M::sin(phi_h), cos_phi_h = M::cos(phi_h);
+    float sin_theta_h = sqrtf(fmaxf(0.0f, 1.0f - cos_theta_h * cos_theta_h));
+    V3 H = mk3(sin_theta_h * cos_phi_h, sin_theta_h * sin_phi_h, cos_theta_h);
+    H = toNormalHemisphere(H, N);
+    return reflect3(-V, H);
+}
+
+// ---- one sample of one pixel: main() of the three shaders ------------------------------------------
+// Returns this frame's colour BEFORE accumulation; primary_id = triangle of the primary hit (-1 miss).
+template <class Cfg, int VARIANT>
+__device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py, uint32_t frame, int& primary_id,
+                                           uint32_t& nrays) {
+    typedef typename Cfg::M M;
+    const DevScene& sc = p.sc;
+    uint32_t seed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + frame * 26699u) | 1u;            // P:73-76
+
+    // ray generation, P:846-850, in strict arithmetic (primary-hit ids must be bit-exact in every mode).
+    // pix = NDC of the fragment centre: ((k + 0.5) / n) * 2 - 1 (vshader.vsh:7-8 interpolated over the quad)
+    float pixx = s_sub(s_mul(s_div(s_add((float)px, 0.5f), (float)p.width), 2.0f), 1.0f);
+    float pixy = s_sub(s_mul(s_div(s_add((float)py, 0.5f), (float)p.height), 2.0f), 1.0f);
+    float a1 = s_div(s_sub(rnd(seed), 0.5f), (float)p.width);
+    float a2 = s_div(s_sub(rnd(seed), 0.5f), (float)p.height);
+    float vx = s_add(pixx, a1), vy = s_add(pixy, a2), vz = -1.5f, vw = 0.0f;
+    const float* m = p.cam;
+    V3 d = mk3(s_add(s_add(s_add(s_mul(m[0], vx), s_mul(m[4], vy)), s_mul(m[8], vz)), s_mul(m[12], vw)),
+               s_add(s_add(s_add(s_mul(m[1], vx), s_mul(m[5], vy)), s_mul(m[9], vz)), s_mul(m[13], vw)),
+               s_add(s_add(s_add(s_mul(m[2], vx), s_mul(m[6], vy)), s_mul(m[10], vz)), s_mul(m[14], vw)));
+    d = s_normalize(d);
+    V3 o = mk3(p.eye[0], p.eye[1], p.eye[2]);
+
+    V3 Le0 = mk3(0, 0, 0), Lo = mk3(0, 0, 0), history = mk3(1, 1, 1);
+    V3 f_r = mk3(0, 0, 0);
+    float cosw = 0.0f, pdf = 1.0f;                   // N·L (cosine_i) and the sampling pdf of the ray in flight
+    Material mat;
+    int bounce = -1;                                  // -1: the ray in flight is the primary ray
+    while (true) {
+        TraceResult tr = trace<Cfg, false>(sc, o, d);
+        nrays++;
+        Hit hit;
+        int mat_id;
+        finalize_hit<Cfg::RAW>(sc, o, d, tr, hit, mat_id);
+        if (bounce < 0) {
+            primary_id = tr.tri;
+            if (!hit.isHit) return sampleHdr<M>(sc, d);                                               // P:857-859
+            load_material<Cfg::RAW>(sc, mat_id, mat);
+            Le0 = mat.emissive;                                                                       // P:862
+        } else if (!hit.isHit) {
+            if (VARIANT == 2) {                                                                       // P:819-830
+                V3 color; float pdf_light;
+                hdr_color_pdf<M>(sc, d, color, pdf_light);
+                float mis_weight = misMixWeight(pdf, pdf_light);
+                Lo = Lo + (history * mis_weight) * color * f_r * cosw / pdf;
+            } else {                                                                                  // O:349-353, D:465-469
+                V3 sky = sampleHdr<M>(sc, d);
+                Lo = Lo + history * sky * f_r * cosw / pdf;
+            }
+            break;
+        } else {
+            load_material<Cfg::RAW>(sc, mat_id, mat);
+            Lo = Lo + history * mat.emissive * f_r * cosw / pdf;                                      // P:833-834
+            history = history * (f_r * cosw / pdf);                                                   // P:837
+        }
+        bounce++;
+        if (bounce >= p.max_bounce) break;
+
+        // ---- next bounce from `hit` with material `mat` ----
+        V3 V = -hit.viewDir, N = hit.normal;
+        V3 L;
+        if (VARIANT == 2) {
+            // light sampling through the hdrCache + shadow ray + MIS, P:770-793
+            float e1 = rnd(seed);
+            float e2 = rnd(seed);
+            V3 Ld = SampleHdr<M>(sc, e1, e2);
+            if (dot(N, Ld) > 0.0f) {
+                TraceResult sh = trace<Cfg, true>(sc, hit.hitPoint, Ld);
+                nrays++;
+                if (sh.tri < 0) {
+                    V3 color; float pdf_light;
+                    hdr_color_pdf<M>(sc, Ld, color, pdf_light);
+                    V3 fl = BRDF_Evaluate_iso<M>(V, N, Ld, mat);
+                    float pdf_b = BRDF_Pdf<M>(V, N, Ld, mat);
+                    float mis_weight = misMixWeight(pdf_light, pdf_b);
+                    Lo = Lo + (history * mis_weight) * color * fl * dot(N, Ld) / pdf_light;
+                }
+            }
+            // BRDF sampling driven by Sobol + Cranley-Patterson, P:795-816
+            float u = sobol((uint32_t)bounce * 2u, (frame + 1u) ^ ((frame + 1u) >> 1));
+            float v = sobol((uint32_t)bounce * 2u + 1u, (frame + 1u) ^ ((frame + 1u) >> 1));
+            cranley_patterson(px, py, u, v);
+            float xi_3 = rnd(seed);
+            L = SampleBRDF<M>(u, v, xi_3, V, N, mat);
+            cosw = dot(N, L);
+            if (cosw <= 0.0f) break;
+            f_r = BRDF_Evaluate_iso<M>(V, N, L, mat);
+            pdf = BRDF_Pdf<M>(V, N, L, mat);
+            if (pdf <= 0.0f) break;                   // the reference traces this ray and then discards it (P:811-816)
+        } else {
+            // uniform hemisphere, O:334-346 / D:448-456
+            float z = rnd(seed);
+            float r = fmaxf(0.0f, sqrtf(1.0f - z * z));
+            float phi = 2.0f * PT_PI * rnd(seed);
+            L = toNormalHemisphere(mk3(r * M::cos(phi), r * M::sin(phi), z), N);
+            pdf = 1.0f / (2.0f * PT_PI);
+            cosw = fmaxf(0.0f, dot(L, N));
+            if (VARIANT == 1) {
+                V3 tangent, bitangent;
+                getTangent(N, tangent, bitangent);
+                f_r = BRDF_Evaluate_aniso<M>(V, N, L, tangent, bitangent, mat);
+            } else {
+                f_r = mat.baseColor / PT_PI;
+            }
+        }
+        o = hit.hitPoint;
+        d = L;
+    }
+    return Le0 + Lo;
+}
+
+// ---- render kernel: one thread per pixel, a warp covers an 8x4 pixel tile, frames looped in registers ----
+#define PT_TILE_W 32     // CTA tile: 4 x 2 warps of 8 x 4 pixels
+#define PT_TILE_H 8
+
+template <class Cfg, int VARIANT>
+__global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ RenderParams p) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int px = p.x0 + blockIdx.x * PT_TILE_W + (warp & 3) * 8 + (lane & 7);
+    const int py = p.y0 + blockIdx.y * PT_TILE_H + (warp >> 2) * 4 + (lane >> 3);
+    uint32_t nrays = 0;
+    if (px < p.x1 && py < p.y1) {
+        const size_t idx = (size_t)py * p.width + px;
+        float4 acc = p.accum[idx];
+        int primary = -1;
+        for (uint32_t f = 0; f < p.n_frames; f++) {
+            const uint32_t frame = p.first_frame + f;
+            V3 c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays);
+            // mix(lastColor, color, 1/(frameCounter+1)), P:868-869 — strict so the running mean is mode-independent
+            float a = s_div(1.0f, (float)(frame + 1u));
+            float b = s_sub(1.0f, a);
+            acc.x = s_add(s_mul(acc.x, b), s_mul(c.x, a));
+            acc.y = s_add(s_mul(acc.y, b), s_mul(c.y, a));
+            acc.z = s_add(s_mul(acc.z, b), s_mul(c.z, a));
+        }
+        acc.w = 1.0f;
+        p.accum[idx] = acc;
+        if (p.primary_ids) p.primary_ids[idx] = primary;
+    }
+    // one atomic per warp for the ray counter
+    for (int o = 16; o > 0; o >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o);
+    if (lane == 0 && nrays) atomicAdd(p.ray_counter, (unsigned long long)nrays);
+}
+
+template <class Cfg>
+cudaError_t launch_render(const RenderParams& p, int variant, cudaStream_t stream) {
+    dim3 grid((p.x1 - p.x0 + PT_TILE_W - 1) / PT_TILE_W, (p.y1 - p.y0 + PT_TILE_H - 1) / PT_TILE_H), block(256);
+    if (variant == 0) render_kernel<Cfg, 0><<<grid, block, 0, stream>>>(p);
+    else if (variant == 1) render_kernel<Cfg, 1><<<grid, block, 0, stream>>>(p);
+    else render_kernel<Cfg, 2><<<grid, block, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace pt

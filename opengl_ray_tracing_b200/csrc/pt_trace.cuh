@@ -1,0 +1,233 @@
+// pt_trace.cuh — ray/box, ray/triangle and the two BVH traversals (the hitBVH of the reference shaders).
+//
+// Reference: ImportanceSampling_LowDiscrepancySequence/shaders/pass1.fsh ("P:") hitTriangle 251-301,
+// hitAABB 303-316, hitArray 319-332, hitBVH 335-382 (same code in the other two shaders).
+//
+// Two traversals with IDENTICAL results:
+//   trace_ref  — the reference algorithm on the reference layout: int stack[256], three 48-byte node
+//                fetches per inner pop, every leaf whose box is touched is fully tested, no culling.
+//   trace_wide — same near-first order, on 64-byte wide nodes (both child boxes in the parent: one fetch
+//                per inner node), packed child refs with leaves folded into their parent, closest-hit
+//                culling against the current best distance, optional any-hit exit for shadow rays, and
+//                48-byte triangle records with the face normal precomputed at upload.
+// Both keep the reference's strict `<` closest-hit rule and leaf/triangle visiting order, so ties are
+// resolved the same way; all tests run in un-fused IEEE arithmetic (pt_common.cuh "strict").
+#pragma once
+#include "pt_common.cuh"
+
+namespace pt {
+
+#define PT_INF 2147483648.0f     // float(INF), P:24
+
+struct Ray {
+    V3 o, d, inv;                // inv = 1/d, computed once per ray (the reference recomputes it per box)
+};
+__device__ __forceinline__ Ray make_ray(V3 o, V3 d) {
+    Ray r; r.o = o; r.d = d;
+    r.inv = mk3(s_div(1.0f, d.x), s_div(1.0f, d.y), s_div(1.0f, d.z));
+    return r;
+}
+
+// hitAABB, P:303-316.  Returns the reference's value (entry distance, or EXIT distance when the origin is
+// inside, or -1) and the entry distance clamped to 0 for culling.
+__device__ __forceinline__ float hit_aabb(const Ray& r, V3 AA, V3 BB, float& entry) {
+    float fx = s_mul(s_sub(BB.x, r.o.x), r.inv.x), nx = s_mul(s_sub(AA.x, r.o.x), r.inv.x);
+    float fy = s_mul(s_sub(BB.y, r.o.y), r.inv.y), ny = s_mul(s_sub(AA.y, r.o.y), r.inv.y);
+    float fz = s_mul(s_sub(BB.z, r.o.z), r.inv.z), nz = s_mul(s_sub(AA.z, r.o.z), r.inv.z);
+    float t1 = fminf(fmaxf(fx, nx), fminf(fmaxf(fy, ny), fmaxf(fz, nz)));
+    float t0 = fmaxf(fminf(fx, nx), fmaxf(fminf(fy, ny), fminf(fz, nz)));
+    entry = fmaxf(t0, 0.0f);
+    return (t1 >= t0) ? ((t0 > 0.0f) ? t0 : t1) : -1.0f;
+}
+
+// hitTriangle, P:251-301, up to the hit decision.  N is the unit face normal normalize(cross(p2-p1,p3-p1))
+// BEFORE the reference's back-face flip: t and the inside test are invariant under N -> -N in IEEE
+// arithmetic (negation commutes exactly with *, + and /), so the flip only sets isInside.
+// `best` implements the strict closest-hit rule: a candidate must have t < best to matter.
+__device__ __forceinline__ bool hit_triangle(const Ray& r, V3 p1, V3 p2, V3 p3, V3 N, float best, float& t_out,
+                                             bool& inside) {
+    float Nd = s_dot(N, r.d);
+    if (fabsf(Nd) < 0.00001f) return false;
+    float t = s_div(s_sub(s_dot(N, p1), s_dot(r.o, N)), Nd);
+    if (t < 0.0005f) return false;
+    if (!(t < best)) return false;
+    V3 P = s_point(r.o, r.d, t);
+    float s1 = s_dot(s_cross(s_sub3(p2, p1), s_sub3(P, p1)), N);
+    float s2 = s_dot(s_cross(s_sub3(p3, p2), s_sub3(P, p2)), N);
+    float s3 = s_dot(s_cross(s_sub3(p1, p3), s_sub3(P, p3)), N);
+    bool pos = (s1 > 0.0f) && (s2 > 0.0f) && (s3 > 0.0f);
+    bool ngt = (s1 < 0.0f) && (s2 < 0.0f) && (s3 < 0.0f);
+    if (!(pos || ngt)) return false;
+    t_out = t;
+    inside = Nd > 0.0f;
+    return true;
+}
+
+struct TraceResult {
+    int tri;                     // -1 = miss
+    float t;
+    bool inside;
+};
+
+// ---- the reference traversal on the reference layout -------------------------------------------
+__device__ __forceinline__ V3 raw3(const float* p) { return mk3(ldg1(p), ldg1(p + 1), ldg1(p + 2)); }
+
+static __device__ __noinline__ TraceResult trace_ref(const DevScene& sc, V3 origin, V3 dir) {
+    Ray r = make_ray(origin, dir);
+    TraceResult res; res.tri = -1; res.t = PT_INF; res.inside = false;
+    int stack[256];                                   // P:340
+    int sp = 0;
+    stack[sp++] = 1;
+    while (sp > 0) {
+        int top = stack[--sp];
+        const float* nd = sc.nodes_raw + 12 * (size_t)top;
+        int left = (int)ldg1(nd), right = (int)ldg1(nd + 1), n = (int)ldg1(nd + 3), index = (int)ldg1(nd + 4);
+        if (n > 0) {                                  // hitArray over [index, index+n-1]
+            for (int i = index; i < index + n; i++) {
+                const float* t = sc.tris_raw + 36 * (size_t)i;
+                V3 p1 = raw3(t), p2 = raw3(t + 3), p3 = raw3(t + 6);
+                V3 N = s_normalize(s_cross(s_sub3(p2, p1), s_sub3(p3, p1)));
+                float tt; bool ins;
+                if (hit_triangle(r, p1, p2, p3, N, res.t, tt, ins)) { res.t = tt; res.tri = i; res.inside = ins; }
+            }
+            continue;
+        }
+        float d1 = PT_INF, d2 = PT_INF, e;
+        if (left > 0) { const float* c = sc.nodes_raw + 12 * (size_t)left; d1 = hit_aabb(r, raw3(c + 6), raw3(c + 9), e); }
+        if (right > 0) { const float* c = sc.nodes_raw + 12 * (size_t)right; d2 = hit_aabb(r, raw3(c + 6), raw3(c + 9), e); }
+        if (sp + 2 > 256) { *sc.error_flag = PT_ERR_STACK; break; }   // the reference would write past stack[256] here
+        if (d1 > 0.0f && d2 > 0.0f) {
+            if (d1 < d2) { stack[sp++] = right; stack[sp++] = left; }
+            else { stack[sp++] = left; stack[sp++] = right; }
+        } else if (d1 > 0.0f) stack[sp++] = left;
+        else if (d2 > 0.0f) stack[sp++] = right;
+    }
+    return res;
+}
+
+// ---- the wide traversal --------------------------------------------------------------------------
+// A child is skipped when its box ENTRY distance exceeds best*(1+2^-16): the slab entry and the plane
+// distance t of a triangle on the box face are different roundings of the same number, so a bare
+// `entry > best` could, in principle, cull the very triangle that defines best's successor.
+#define PT_CULL_SLACK 1.0000153f
+// Deferred-subtree stack capacity = the reference's own `int stack[256]` (P:340).  Local memory is
+// interleaved per lane, so only the slots a ray actually touches cost cache lines.
+#define PT_STACK 256
+
+template <bool ANYHIT, int STACK>
+__device__ __forceinline__ TraceResult trace_wide(const DevScene& sc, V3 origin, V3 dir) {
+    Ray r = make_ray(origin, dir);
+    TraceResult res; res.tri = -1; res.t = PT_INF; res.inside = false;
+    float cull = PT_INF;
+    uint32_t stack_ref[STACK];
+    float stack_t[STACK];
+    int sp = 0;
+    uint32_t ref = sc.root_ref;
+    while (true) {
+        if (ref_count(ref)) {
+            // leaf: triangles first .. first+count-1 in order (hitArray)
+            uint32_t first = ref_index(ref), cnt = ref_count(ref);
+            for (uint32_t i = first; i < first + cnt; i++) {
+                const float4* g = sc.trigeo + 3 * (size_t)i;
+                float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2);
+                float tt; bool ins;
+                if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), mk3(a.w, b.w, c.w),
+                                 res.t, tt, ins)) {
+                    res.t = tt; res.tri = (int)i; res.inside = ins;
+                    if (ANYHIT) return res;
+                    cull = s_mul(tt, PT_CULL_SLACK);
+                }
+            }
+        } else {
+            const float4* w = sc.wnodes + 4 * (size_t)ref_index(ref);
+            float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
+            float e1, e2;
+            float d1 = hit_aabb(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), e1);
+            float d2 = hit_aabb(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), e2);
+            uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+            bool h1 = (d1 > 0.0f) && (lref != PT_REF_NONE), h2 = (d2 > 0.0f) && (rref != PT_REF_NONE);
+            bool g1 = h1 && (e1 <= cull), g2 = h2 && (e2 <= cull);
+            if (h1 && h2) {
+                // near child first (P:367-374): left iff d1 < d2
+                bool left_first = d1 < d2;
+                uint32_t nref = left_first ? lref : rref, fref = left_first ? rref : lref;
+                float ne = left_first ? e1 : e2, fe = left_first ? e2 : e1;
+                bool ng = left_first ? g1 : g2, fg = left_first ? g2 : g1;
+                if (fg) {
+                    if (ng) {
+                        if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; break; }
+                        stack_ref[sp] = fref; stack_t[sp] = fe; sp++; ref = nref; continue;
+                    }
+                    ref = fref; continue;
+                }
+                if (ng) { ref = nref; continue; }
+                (void)ne;
+            } else if (g1) { ref = lref; continue; }
+            else if (g2) { ref = rref; continue; }
+        }
+        // pop the next subtree still worth visiting
+        bool found = false;
+        while (sp > 0) {
+            sp--;
+            if (stack_t[sp] <= cull) { ref = stack_ref[sp]; found = true; break; }
+        }
+        if (!found) break;
+    }
+    return res;
+}
+
+// ---- what the shader's HitResult carries for the winning triangle (P:285-299) -------------------
+template <bool RAW_LAYOUT>
+__device__ __forceinline__ void finalize_hit(const DevScene& sc, V3 origin, V3 dir, const TraceResult& tr, Hit& h,
+                                             int& mat_id) {
+    h.isHit = tr.tri >= 0;
+    h.tri = tr.tri;
+    h.distance = tr.t;
+    h.isInside = tr.inside;
+    h.viewDir = dir;
+    mat_id = 0;
+    if (!h.isHit) return;
+    V3 p1, p2, p3, n1, n2, n3;
+    if (RAW_LAYOUT) {
+        const float* t = sc.tris_raw + 36 * (size_t)tr.tri;
+        p1 = raw3(t); p2 = raw3(t + 3); p3 = raw3(t + 6); n1 = raw3(t + 9); n2 = raw3(t + 12); n3 = raw3(t + 15);
+        mat_id = tr.tri;                              // material read from the triangle record itself
+    } else {
+        const float4* g = sc.trigeo + 3 * (size_t)tr.tri;
+        const float4* s = sc.trishade + 3 * (size_t)tr.tri;
+        float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2), u = ldg4(s), v = ldg4(s + 1), w = ldg4(s + 2);
+        p1 = mk3(a.x, a.y, a.z); p2 = mk3(b.x, b.y, b.z); p3 = mk3(c.x, c.y, c.z);
+        n1 = mk3(u.x, u.y, u.z); n2 = mk3(v.x, v.y, v.z); n3 = mk3(w.x, w.y, w.z);
+        mat_id = __float_as_int(u.w);
+    }
+    V3 P = s_point(origin, dir, tr.t);
+    h.hitPoint = P;
+    // P:293-297 — barycentrics from x and y only, with the author's 5e-5 offsets
+    float alpha = (-(P.x - p2.x) * (p3.y - p2.y) + (P.y - p2.y) * (p3.x - p2.x)) /
+                  (-(p1.x - p2.x - 0.00005f) * (p3.y - p2.y + 0.00005f) + (p1.y - p2.y + 0.00005f) * (p3.x - p2.x + 0.00005f));
+    float beta = (-(P.x - p3.x) * (p1.y - p3.y) + (P.y - p3.y) * (p1.x - p3.x)) /
+                 (-(p2.x - p3.x - 0.00005f) * (p1.y - p3.y + 0.00005f) + (p2.y - p3.y + 0.00005f) * (p1.x - p3.x + 0.00005f));
+    float gama = 1.0f - alpha - beta;
+    V3 Ns = normalize(n1 * alpha + n2 * beta + n3 * gama);
+    h.normal = tr.inside ? -Ns : Ns;
+}
+
+template <bool RAW_LAYOUT>
+__device__ __forceinline__ void load_material(const DevScene& sc, int mat_id, Material& m) {
+    if (RAW_LAYOUT) {                                 // getMaterial, P:207-232: texels 6..11 of the triangle
+        const float* t = sc.tris_raw + 36 * (size_t)mat_id + 18;
+        m.emissive = raw3(t); m.baseColor = raw3(t + 3);
+        m.subsurface = ldg1(t + 6); m.metallic = ldg1(t + 7); m.specular = ldg1(t + 8);
+        m.specularTint = ldg1(t + 9); m.roughness = ldg1(t + 10); m.anisotropic = ldg1(t + 11);
+        m.sheen = ldg1(t + 12); m.sheenTint = ldg1(t + 13); m.clearcoat = ldg1(t + 14); m.clearcoatGloss = ldg1(t + 15);
+    } else {
+        const float4* p = sc.materials + 4 * (size_t)mat_id;
+        float4 a = ldg4(p), b = ldg4(p + 1), c = ldg4(p + 2), d = ldg4(p + 3);
+        m.emissive = mk3(a.x, a.y, a.z); m.subsurface = a.w;
+        m.baseColor = mk3(b.x, b.y, b.z); m.metallic = b.w;
+        m.specular = c.x; m.specularTint = c.y; m.roughness = c.z; m.anisotropic = c.w;
+        m.sheen = d.x; m.sheenTint = d.y; m.clearcoat = d.z; m.clearcoatGloss = d.w;
+    }
+}
+
+}  // namespace pt

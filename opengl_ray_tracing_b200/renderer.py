@@ -1,0 +1,173 @@
+"""ctypes mirror of libpt.so (include/pt.h): the CUDA path tracer behind the reference's draw loop.
+
+``PathTracer`` plays the role of the reference's ``RenderPass pass1`` + ``display()``
+(ImportanceSampling_LowDiscrepancySequence/main.cpp:76-133, 659-709): upload once, then per frame set the
+camera uniforms and draw.  All compute is in the CUDA library; there is no CPU fallback — if libpt.so is
+missing or no CUDA device is visible, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libpt.so")
+_lib = None
+
+LAMBERT, DISNEY_UNIFORM, DISNEY_IS_MIS = 0, 1, 2
+MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE = 0, 1, 2
+DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
+
+EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_render_spp",
+           "pt_clear", "pt_readback", "pt_readback_primary_ids", "pt_framebuffer_device_ptr", "pt_stream",
+           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_last_error",
+           "pt_build_info"]
+
+
+class PtConfig(C.Structure):
+    _fields_ = [("variant", C.c_int), ("width", C.c_int), ("height", C.c_int), ("max_bounce", C.c_int),
+                ("device", C.c_int), ("mode", C.c_int)]
+
+
+class PtStats(C.Structure):
+    _fields_ = [("rays", C.c_ulonglong), ("samples", C.c_ulonglong), ("render_ms", C.c_double),
+                ("launches", C.c_ulonglong), ("max_stack_depth", C.c_int), ("n_inner_nodes", C.c_int),
+                ("n_materials", C.c_int)]
+
+
+class PtError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise PtError("libpt.so is not built (python __graft_entry__.py build); there is no CPU fallback")
+    L = C.CDLL(_LIB_PATH)
+    vp, f32p = C.c_void_p, C.POINTER(C.c_float)
+    sig = {
+        "pt_create": (C.c_int, [C.POINTER(PtConfig), C.POINTER(vp)]),
+        "pt_destroy": (C.c_int, [vp]),
+        "pt_upload_scene": (C.c_int, [vp, f32p, C.c_int, f32p, C.c_int, f32p, f32p, C.c_int, C.c_int]),
+        "pt_set_camera": (C.c_int, [vp, f32p, f32p]),
+        "pt_set_region": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int]),
+        "pt_render_spp": (C.c_int, [vp, C.c_uint, C.c_uint]),
+        "pt_clear": (C.c_int, [vp]),
+        "pt_readback": (C.c_int, [vp, vp, C.c_size_t]),
+        "pt_readback_primary_ids": (C.c_int, [vp, vp, C.c_size_t]),
+        "pt_framebuffer_device_ptr": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
+        "pt_stream": (C.c_int, [vp, C.POINTER(vp)]),
+        "pt_scale_framebuffer": (C.c_int, [vp, C.c_float]),
+        "pt_synchronize": (C.c_int, [vp]),
+        "pt_get_stats": (C.c_int, [vp, C.POINTER(PtStats)]),
+        "pt_reset_stats": (C.c_int, [vp]),
+        "pt_last_error": (C.c_char_p, []),
+        "pt_build_info": (C.c_char_p, []),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise PtError("%s failed (%d): %s" % (what, rc, lib().pt_last_error().decode("utf-8", "replace")))
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float)) if a is not None else None
+
+
+class PathTracer:
+    """pass1 of the reference (shader variant ``variant``) on CUDA device ``device``."""
+
+    def __init__(self, width, height, variant=DISNEY_IS_MIS, max_bounce=0, device=0, mode=MODE_FAST):
+        self.width, self.height, self.variant, self.mode = width, height, variant, mode
+        cfg = PtConfig(variant, width, height, max_bounce, device, mode)
+        h = C.c_void_p()
+        _check(lib().pt_create(C.byref(cfg), C.byref(h)), "pt_create")
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().pt_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def upload_scene(self, tris, nodes, hdr, hdrCache=None):
+        """glBufferData x2 + glTexImage2D x2 (M:825-853).  tris [T,36], nodes [N,12], hdr/hdrCache [h,w,3]."""
+        t, n, hd = _f32(tris).reshape(-1, 36), _f32(nodes).reshape(-1, 12), _f32(hdr)
+        hc = _f32(hdrCache) if hdrCache is not None else None
+        assert hd.ndim == 3 and hd.shape[2] == 3, "hdr must be [h, w, 3]"
+        if hc is not None:
+            assert hc.shape == hd.shape, "hdrCache must have the HDR map's shape"
+        _check(lib().pt_upload_scene(self._h, _fp(t), len(t), _fp(n), len(n), _fp(hd), _fp(hc), hd.shape[1], hd.shape[0]),
+               "pt_upload_scene")
+
+    def set_camera(self, eye, cameraRotate):
+        e, c = _f32(eye).reshape(3), _f32(cameraRotate).reshape(16)
+        _check(lib().pt_set_camera(self._h, _fp(e), _fp(c)), "pt_set_camera")
+
+    def set_region(self, x0, y0, x1, y1):
+        _check(lib().pt_set_region(self._h, x0, y0, x1, y1), "pt_set_region")
+
+    def render_spp(self, first_frame, n_frames):
+        """frameCounter = first_frame .. first_frame+n_frames-1; asynchronous."""
+        _check(lib().pt_render_spp(self._h, first_frame, n_frames), "pt_render_spp")
+
+    def clear(self):
+        _check(lib().pt_clear(self._h), "pt_clear")
+
+    def synchronize(self):
+        _check(lib().pt_synchronize(self._h), "pt_synchronize")
+
+    def readback(self, out=None) -> np.ndarray:
+        """float32 [H, W, 4]; row 0 = bottom row."""
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.float32)
+        _check(lib().pt_readback(self._h, out.ctypes.data, out.nbytes), "pt_readback")
+        return out
+
+    def readback_into(self, host_ptr, nbytes):
+        _check(lib().pt_readback(self._h, host_ptr, nbytes), "pt_readback")
+
+    def readback_primary_ids(self) -> np.ndarray:
+        out = np.empty((self.height, self.width), np.int32)
+        _check(lib().pt_readback_primary_ids(self._h, out.ctypes.data, out.nbytes), "pt_readback_primary_ids")
+        return out
+
+    def framebuffer_device_ptr(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        _check(lib().pt_framebuffer_device_ptr(self._h, C.byref(p), C.byref(n)), "pt_framebuffer_device_ptr")
+        return p.value, n.value
+
+    def stream(self):
+        s = C.c_void_p()
+        _check(lib().pt_stream(self._h, C.byref(s)), "pt_stream")
+        return s.value or 0
+
+    def scale_framebuffer(self, scale):
+        _check(lib().pt_scale_framebuffer(self._h, scale), "pt_scale_framebuffer")
+
+    def stats(self) -> dict:
+        st = PtStats()
+        _check(lib().pt_get_stats(self._h, C.byref(st)), "pt_get_stats")
+        return {k: getattr(st, k) for k, _ in PtStats._fields_}
+
+    def reset_stats(self):
+        _check(lib().pt_reset_stats(self._h), "pt_reset_stats")
+
+
+def build_info() -> str:
+    return lib().pt_build_info().decode()
