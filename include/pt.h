@@ -37,13 +37,17 @@ extern "C" {
 #define PT_VARIANT_DISNEY_IS_MIS  2   /* ImportanceSampling_…/shaders/pass1.fsh — maxBounce 2 (P:861) */
 
 /* arithmetic mode */
-#define PT_MODE_FAST          0   /* wide-node culled traversal; CUDA fast math + FMA in shading; exact (IEEE,
-                                     un-fused) ray generation and ray/box/triangle tests */
+#define PT_MODE_FAST          0   /* production: culled traversal of a binned-SAH topology over the reference's leaves
+                                     (exact ties re-traced in reference order); CUDA fast math + FMA in shading;
+                                     exact (IEEE, un-fused) ray generation and ray/box/triangle tests */
 #define PT_MODE_PARITY_REF    1   /* reference layout (48 B nodes, 144 B triangles), reference traversal without
                                      culling, no FMA, include/ptmath.h transcendental functions: bit-identical to
                                      the CPU oracle */
-#define PT_MODE_PARITY_WIDE   2   /* the fast traversal + data layout under the parity arithmetic: bit-identical
-                                     to the oracle too — proves the traversal restructuring changes no result */
+#define PT_MODE_PARITY_WIDE   2   /* the wide-node data layout + culled traversal of the REFERENCE topology under the
+                                     parity arithmetic: bit-identical to the oracle */
+#define PT_MODE_PARITY_FAST   3   /* PT_MODE_FAST's traversal (binned-SAH topology, tie fallback) under the parity
+                                     arithmetic: bit-identical to the oracle too — proves that neither the layout nor
+                                     the topology change any result */
 
 typedef struct PtConfig {
     int variant;        /* PT_VARIANT_* */
@@ -61,6 +65,9 @@ typedef struct PtStats {
     int max_stack_depth;              /* deepest traversal stack the uploaded BVH can need */
     int n_inner_nodes;                /* wide nodes built at upload */
     int n_materials;                  /* distinct materials found at upload */
+    int fast_tree_depth;              /* depth of the traversal topology built at upload (pt_build.cpp) */
+    int n_fast_inner;                 /* its inner-node count */
+    double upload_build_ms;           /* host time spent building that topology in the last pt_upload_scene */
 } PtStats;
 
 typedef struct pt_ctx pt_ctx;
@@ -86,10 +93,23 @@ int pt_set_camera(pt_ctx* ctx, const float eye[3], const float cameraRotate[16])
    multi-GPU runs.  Default: the whole image.  (No reference equivalent: glViewport is always full, M:125.) */
 int pt_set_region(pt_ctx* ctx, int x0, int y0, int x1, int y1);
 
+/* Interleaved tile split in ONE launch: the image rows are cut into bands of 8 rows (one CTA tile row); this
+   context renders band b iff b % world == rank.  world = 1 (default) renders every band.  Applies on top of the
+   region rectangle.  Bands interleave so that sky rows and geometry rows spread evenly over the GPUs. */
+int pt_set_band_interleave(pt_ctx* ctx, int world, int rank);
+
 /* pass1.draw() + pass2.draw() for frameCounter = first_frame .. first_frame + n_frames - 1 (M:680, M:704-705):
    one sample per pixel per frame, running mean mix(last, colour, 1/(frame+1)) (P:868-869) kept in the fp32
    framebuffer.  Asynchronous on the context's stream. */
 int pt_render_spp(pt_ctx* ctx, unsigned first_frame, unsigned n_frames);
+
+/* Sample-split multi-GPU form: renders frameCounter = first_frame + k*stride, k = 0 .. n_frames-1.
+   accumulate = PT_ACC_MEAN: the reference's running mean (needs stride 1 and contiguous calls from frame 0);
+   accumulate = PT_ACC_SUM: framebuffer += colour, so that per-GPU partial sums can be added (NCCL reduce) and
+   divided by the total frame count afterwards (pt_scale_framebuffer). */
+#define PT_ACC_MEAN 0
+#define PT_ACC_SUM  1
+int pt_render_frames(pt_ctx* ctx, unsigned first_frame, unsigned n_frames, unsigned stride, int accumulate);
 
 /* Zeroes the framebuffer (frameCounter = 0 after a camera move, M:718, M:737, makes the first mix() discard it). */
 int pt_clear(pt_ctx* ctx);
@@ -103,8 +123,7 @@ int pt_readback_primary_ids(pt_ctx* ctx, int* ids, size_t bytes);
    host (torch.distributed / NCCL) can reduce or gather in place without a host round trip. */
 int pt_framebuffer_device_ptr(pt_ctx* ctx, void** dptr, size_t* bytes);
 int pt_stream(pt_ctx* ctx, void** cuda_stream);
-/* Multiplies the framebuffer by `scale` and optionally applies pass3.fsh's tone map (pass3.fsh:14-24) into
-   rgba8 (may be NULL) — the epilogue after a sample-split NCCL sum. */
+/* Multiplies the framebuffer's rgb by `scale` — the epilogue after a sample-split NCCL sum. */
 int pt_scale_framebuffer(pt_ctx* ctx, float scale);
 
 int pt_synchronize(pt_ctx* ctx);

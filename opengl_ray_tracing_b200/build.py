@@ -65,9 +65,13 @@ def build_pt(force=False):
         if force or _stale(obj, [src] + hdrs):
             _run(["nvcc", *ARCH, *NVCC_COMMON, *extra, "-c", src, "-o", obj], log=os.path.join(BUILD, name + ".ptxas.log"))
         objs.append(obj)
+    src, obj = os.path.join(CSRC, "pt_build.cpp"), os.path.join(BUILD, "pt_build.o")
+    if force or _stale(obj, [src]):
+        _run(["g++", "-std=c++17", "-O3", "-fopenmp", "-fPIC", "-Wall", "-Wextra", "-c", src, "-o", obj])
+    objs.append(obj)
     out = os.path.join(HERE, "libpt.so")
     if force or _stale(out, objs):
-        _run(["nvcc", *ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-o", out])
+        _run(["nvcc", *ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-lgomp", "-o", out])
     return out
 
 

@@ -15,6 +15,8 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <thread>
+#include <chrono>
 #include <unordered_map>
 #include <vector>
 
@@ -22,7 +24,9 @@
 #include "pt_common.cuh"
 
 namespace pt {
-cudaError_t launch_parity(const RenderParams& p, int variant, bool reference_layout, cudaStream_t stream);
+cudaError_t launch_parity(const RenderParams& p, int variant, int which, cudaStream_t stream);
+struct FastTree { std::vector<float> wnodes; uint32_t root_ref = 0; int depth = 0; int n_leaves = 0; };
+void build_fast_tree(const float* nodes_raw, int nNodes, FastTree& out, int threads);
 cudaError_t launch_fast(const RenderParams& p, int variant, cudaStream_t stream);
 }
 
@@ -46,13 +50,16 @@ struct pt_ctx {
     int* error_flag = nullptr;
     // scene
     bool has_scene = false;
+    int fast_depth = 0, n_fast_inner = 0;
+    double build_ms = 0.0;
     float *tris_raw = nullptr, *nodes_raw = nullptr;
-    float4 *wnodes = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr;
+    float4 *wnodes = nullptr, *wnodes_fast = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr;
     pt::DevScene sc;
     // camera + region
     float eye[3] = {0, 0, 4};
     float cam[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 4, 1};
     int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    int band_world = 1, band_rank = 0;
     // stats
     unsigned long long samples = 0, launches = 0;
     double render_ms = 0.0;
@@ -136,10 +143,10 @@ struct MatHash {
 };
 
 void free_scene(pt_ctx* c) {
-    cudaFree(c->tris_raw); cudaFree(c->nodes_raw); cudaFree(c->wnodes); cudaFree(c->trigeo); cudaFree(c->trishade);
+    cudaFree(c->tris_raw); cudaFree(c->nodes_raw); cudaFree(c->wnodes); cudaFree(c->wnodes_fast); cudaFree(c->trigeo); cudaFree(c->trishade);
     cudaFree(c->materials); cudaFree(c->hdr4); cudaFree(c->cache4);
     c->tris_raw = c->nodes_raw = nullptr;
-    c->wnodes = c->trigeo = c->trishade = c->materials = c->hdr4 = c->cache4 = nullptr;
+    c->wnodes = c->wnodes_fast = c->trigeo = c->trishade = c->materials = c->hdr4 = c->cache4 = nullptr;
     c->has_scene = false;
 }
 
@@ -188,7 +195,7 @@ const char* pt_build_info(void) {
 int pt_create(const PtConfig* cfg, pt_ctx** out) {
     if (!cfg || !out) return fail(PT_EINVAL, "pt_create: null argument");
     if (cfg->variant < 0 || cfg->variant > 2) return fail(PT_EINVAL, "pt_create: variant must be 0, 1 or 2");
-    if (cfg->mode < 0 || cfg->mode > 2) return fail(PT_EINVAL, "pt_create: mode must be PT_MODE_FAST/PARITY_REF/PARITY_WIDE");
+    if (cfg->mode < 0 || cfg->mode > 3) return fail(PT_EINVAL, "pt_create: mode must be one of PT_MODE_*");
     if (cfg->width <= 0 || cfg->height <= 0 || cfg->width > 16384 || cfg->height > 16384)
         return fail(PT_EINVAL, "pt_create: width/height out of range");
     int mb = cfg->max_bounce > 0 ? cfg->max_bounce : (cfg->variant == PT_VARIANT_DISNEY_UNIFORM ? 5 : 2);
@@ -284,7 +291,8 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     float* d_tmp = nullptr;
     void* d_scan = nullptr;
     size_t scan_bytes = 0;
-    int nInner = 0;
+    int nInner = 0, nFastInner = 0, fast_depth = 0;
+    uint32_t root_fast = 0;
     int rc = PT_OK;
 #define CKU(call)                                                                                  \
     do {                                                                                           \
@@ -315,6 +323,19 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         k_build_wide<<<(nNodes + 255) / 256, 256, 0, st>>>(c->nodes_raw, nNodes, d_flag, d_widx, c->wnodes);
         CKU(cudaGetLastError());
     }
+    // traversal topology: binned SAH over the reference's leaves (host build, pt_build.cpp)
+    {
+        pt::FastTree ft;
+        int hw = (int)std::thread::hardware_concurrency();
+        auto t0 = std::chrono::steady_clock::now();
+        pt::build_fast_tree(nodes, nNodes, ft, hw > 0 ? (hw > 32 ? 32 : hw) : 1);
+        c->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        root_fast = ft.root_ref; fast_depth = ft.depth; nFastInner = (int)(ft.wnodes.size() / 16);
+        CKU(cudaMalloc(&c->wnodes_fast, (ft.wnodes.empty() ? 16 : ft.wnodes.size()) * sizeof(float)));
+        if (!ft.wnodes.empty())
+            CKU(cudaMemcpyAsync(c->wnodes_fast, ft.wnodes.data(), ft.wnodes.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+        CKU(cudaStreamSynchronize(st));               // ft goes out of scope
+    }
     // triangles
     CKU(cudaMalloc(&d_matid, (size_t)nTriangles * sizeof(int)));
     CKU(cudaMemcpyAsync(d_matid, mat_id.data(), (size_t)nTriangles * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -340,7 +361,8 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     CKU(cudaStreamSynchronize(st));
     {
         pt::DevScene& s = c->sc;
-        s.tris_raw = c->tris_raw; s.nodes_raw = c->nodes_raw; s.wnodes = c->wnodes; s.trigeo = c->trigeo;
+        s.tris_raw = c->tris_raw; s.nodes_raw = c->nodes_raw; s.wnodes = c->wnodes; s.wnodes_fast = c->wnodes_fast; s.trigeo = c->trigeo;
+        s.root_fast = root_fast; c->fast_depth = fast_depth; c->n_fast_inner = nFastInner;
         s.trishade = c->trishade; s.materials = c->materials; s.hdr4 = c->hdr4; s.cache4 = c->cache4;
         s.nTriangles = nTriangles; s.nNodes = nNodes; s.nInner = nInner; s.nMaterials = nMaterials;
         s.hdrW = hdrW; s.hdrH = hdrH; s.stack_depth = depth; s.error_flag = c->error_flag;
@@ -372,6 +394,13 @@ int pt_set_region(pt_ctx* c, int x0, int y0, int x1, int y1) {
     return PT_OK;
 }
 
+int pt_set_band_interleave(pt_ctx* c, int world, int rank) {
+    if (!c) return fail(PT_EINVAL, "pt_set_band_interleave: null context");
+    if (world < 1 || rank < 0 || rank >= world) return fail(PT_EINVAL, "pt_set_band_interleave: need 0 <= rank < world");
+    c->band_world = world; c->band_rank = rank;
+    return PT_OK;
+}
+
 static int collect_timing(pt_ctx* c) {
     if (!c->timing_pending) return PT_OK;
     float ms = 0.f;
@@ -390,7 +419,13 @@ static int collect_timing(pt_ctx* c) {
 }
 
 int pt_render_spp(pt_ctx* c, unsigned first_frame, unsigned n_frames) {
+    return pt_render_frames(c, first_frame, n_frames, 1u, PT_ACC_MEAN);
+}
+
+int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigned stride, int accumulate) {
     if (!c) return fail(PT_EINVAL, "pt_render_spp: null context");
+    if (stride == 0 || (accumulate != PT_ACC_MEAN && accumulate != PT_ACC_SUM)) return fail(PT_EINVAL, "pt_render_frames: bad stride/accumulate");
+    if (accumulate == PT_ACC_MEAN && stride != 1) return fail(PT_EINVAL, "pt_render_frames: the running mean needs stride 1");
     if (!c->has_scene) return fail(PT_ENOSCENE, "pt_render_spp: no scene uploaded");
     if (n_frames == 0) return PT_OK;
     CK(cudaSetDevice(c->cfg.device));
@@ -402,17 +437,23 @@ int pt_render_spp(pt_ctx* c, unsigned first_frame, unsigned n_frames) {
     std::memcpy(p.cam, c->cam, 64);
     p.width = c->cfg.width; p.height = c->cfg.height;
     p.x0 = c->x0; p.y0 = c->y0; p.x1 = c->x1; p.y1 = c->y1;
-    p.first_frame = first_frame; p.n_frames = n_frames;
+    p.band_world = c->band_world; p.band_rank = c->band_rank;
+    p.first_frame = first_frame; p.n_frames = n_frames; p.frame_stride = stride; p.accumulate_sum = accumulate;
     p.max_bounce = c->cfg.max_bounce;
     p.accum = c->accum; p.primary_ids = c->primary_ids; p.ray_counter = c->ray_counter;
     CK(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e = c->cfg.mode == PT_MODE_FAST ? pt::launch_fast(p, c->cfg.variant, c->stream)
-                                                 : pt::launch_parity(p, c->cfg.variant, c->cfg.mode == PT_MODE_PARITY_REF, c->stream);
+                                                 : pt::launch_parity(p, c->cfg.variant, c->cfg.mode, c->stream);
     if (e != cudaSuccess) return fail(PT_ECUDA, std::string("render kernel launch: ") + cudaGetErrorString(e));
     CK(cudaEventRecord(c->ev1, c->stream));
     c->timing_pending = true;
     c->launches += 1;
-    c->samples += (unsigned long long)(c->x1 - c->x0) * (c->y1 - c->y0) * n_frames;
+    {
+        unsigned long long rows = 0;
+        for (int y = c->y0, b = 0; y < c->y1; y += 8, b++)
+            if (b % c->band_world == c->band_rank) rows += (unsigned long long)((c->y1 - y) < 8 ? (c->y1 - y) : 8);
+        c->samples += (unsigned long long)(c->x1 - c->x0) * rows * n_frames;
+    }
     return PT_OK;
 }
 
@@ -487,6 +528,7 @@ int pt_get_stats(pt_ctx* c, PtStats* out) {
     out->max_stack_depth = c->has_scene ? c->sc.stack_depth : 0;
     out->n_inner_nodes = c->has_scene ? c->sc.nInner : 0;
     out->n_materials = c->has_scene ? c->sc.nMaterials : 0;
+    out->fast_tree_depth = c->fast_depth; out->n_fast_inner = c->n_fast_inner; out->upload_build_ms = c->build_ms;
     return PT_OK;
 }
 

@@ -73,7 +73,8 @@ struct DevScene {
     const float* tris_raw;      // nTriangles x 36 floats  (Triangle_encoded)
     const float* nodes_raw;     // nNodes x 12 floats      (BVHNode_encoded)
     // traversal layout built on the device at upload
-    const float4* wnodes;       // nInner x 4 float4 (64 B): child boxes + packed child refs
+    const float4* wnodes;       // nInner x 4 float4 (64 B): child boxes + packed child refs, REFERENCE topology
+    const float4* wnodes_fast;  // same record format, binned-SAH topology over the reference's leaves (pt_build.cpp)
     const float4* trigeo;       // nTriangles x 3 float4 (48 B): (p1,N.x) (p2,N.y) (p3,N.z), N = unit face normal
     const float4* trishade;     // nTriangles x 3 float4 (48 B): (n1, matId) (n2, -) (n3, -)
     const float4* materials;    // nMaterials x 4 float4 (64 B)
@@ -81,7 +82,7 @@ struct DevScene {
     const float4* cache4;       // hdrH x hdrW float4 (x/w, y/h, pdf, 0) or null
     int nTriangles, nNodes, nInner, nMaterials;
     int hdrW, hdrH;
-    uint32_t root_ref;
+    uint32_t root_ref, root_fast;
     int stack_depth;            // depth of the tree = worst-case traversal stack
     int* error_flag;            // set to PT_ERR_* by a kernel that had to give up (checked at the next sync)
 };
@@ -93,7 +94,9 @@ struct RenderParams {
     float cam[16];              // column-major cameraRotate
     int width, height;
     int x0, y0, x1, y1;         // region
-    unsigned first_frame, n_frames;
+    int band_world, band_rank;  // interleaved 8-row bands: this launch owns band b iff b % band_world == band_rank
+    unsigned first_frame, n_frames, frame_stride;
+    int accumulate_sum;         // 0: running mean (P:869), 1: += colour
     int max_bounce;
     float4* accum;              // W*H float4, row 0 = bottom
     int* primary_ids;           // W*H

@@ -5,8 +5,10 @@
 #include "pt_shade.cuh"
 
 namespace pt {
-cudaError_t launch_parity(const RenderParams& p, int variant, bool reference_layout, cudaStream_t stream) {
-    return reference_layout ? launch_render<CfgParityRef>(p, variant, stream)
-                            : launch_render<CfgParityWide>(p, variant, stream);
+// which: 1 = PT_MODE_PARITY_REF, 2 = PT_MODE_PARITY_WIDE, 3 = PT_MODE_PARITY_FAST
+cudaError_t launch_parity(const RenderParams& p, int variant, int which, cudaStream_t stream) {
+    if (which == 1) return launch_render<CfgParityRef>(p, variant, stream);
+    if (which == 2) return launch_render<CfgParityWide>(p, variant, stream);
+    return launch_render<CfgParityFast>(p, variant, stream);
 }
 }  // namespace pt

@@ -42,14 +42,20 @@ struct MathFast {                 // SFU approximations where CUDA has them
     static __device__ __forceinline__ float log(float a) { return __logf(a); }
     static __device__ __forceinline__ float pow(float a, float b) { return __powf(a, b); }
 };
-struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  };
-struct CfgParityWide { typedef MathExact M; static const bool RAW = false; };
-struct CfgFast       { typedef MathFast  M; static const bool RAW = false; };
+struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; };
+struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; };
+struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  };
+struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  };
 
 template <class Cfg, bool ANYHIT>
 __device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d) {
     if (Cfg::RAW) return trace_ref(sc, o, d);
-    else return trace_wide<ANYHIT, PT_STACK>(sc, o, d);
+    if (Cfg::FAST_TREE) {
+        TraceResult tr = trace_fast<ANYHIT, PT_STACK>(sc, o, d);
+        if (!ANYHIT && tr.tri == -2) tr = trace_wide_fallback(sc, o, d);   // exact tie: let the reference order decide
+        return tr;
+    }
+    return trace_wide<ANYHIT, PT_STACK>(sc, o, d);
 }
 
 // ---- RNG and QMC -----------------------------------------------------------------------------------
@@ -408,21 +414,25 @@ template <class Cfg, int VARIANT>
 __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ RenderParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int px = p.x0 + blockIdx.x * PT_TILE_W + (warp & 3) * 8 + (lane & 7);
-    const int py = p.y0 + blockIdx.y * PT_TILE_H + (warp >> 2) * 4 + (lane >> 3);
+    const int py = p.y0 + (blockIdx.y * p.band_world + p.band_rank) * PT_TILE_H + (warp >> 2) * 4 + (lane >> 3);
     uint32_t nrays = 0;
     if (px < p.x1 && py < p.y1) {
         const size_t idx = (size_t)py * p.width + px;
         float4 acc = p.accum[idx];
         int primary = -1;
         for (uint32_t f = 0; f < p.n_frames; f++) {
-            const uint32_t frame = p.first_frame + f;
+            const uint32_t frame = p.first_frame + f * p.frame_stride;
             V3 c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays);
-            // mix(lastColor, color, 1/(frameCounter+1)), P:868-869 — strict so the running mean is mode-independent
-            float a = s_div(1.0f, (float)(frame + 1u));
-            float b = s_sub(1.0f, a);
-            acc.x = s_add(s_mul(acc.x, b), s_mul(c.x, a));
-            acc.y = s_add(s_mul(acc.y, b), s_mul(c.y, a));
-            acc.z = s_add(s_mul(acc.z, b), s_mul(c.z, a));
+            if (p.accumulate_sum) {
+                acc.x = s_add(acc.x, c.x); acc.y = s_add(acc.y, c.y); acc.z = s_add(acc.z, c.z);
+            } else {
+                // mix(lastColor, color, 1/(frameCounter+1)), P:868-869 — strict so the running mean is mode-independent
+                float a = s_div(1.0f, (float)(frame + 1u));
+                float b = s_sub(1.0f, a);
+                acc.x = s_add(s_mul(acc.x, b), s_mul(c.x, a));
+                acc.y = s_add(s_mul(acc.y, b), s_mul(c.y, a));
+                acc.z = s_add(s_mul(acc.z, b), s_mul(c.z, a));
+            }
         }
         acc.w = 1.0f;
         p.accum[idx] = acc;
@@ -435,7 +445,10 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
 
 template <class Cfg>
 cudaError_t launch_render(const RenderParams& p, int variant, cudaStream_t stream) {
-    dim3 grid((p.x1 - p.x0 + PT_TILE_W - 1) / PT_TILE_W, (p.y1 - p.y0 + PT_TILE_H - 1) / PT_TILE_H), block(256);
+    const int bands = (p.y1 - p.y0 + PT_TILE_H - 1) / PT_TILE_H;                     // 8-row bands in the region
+    const int owned = bands > p.band_rank ? (bands - p.band_rank + p.band_world - 1) / p.band_world : 0;
+    if (owned == 0) return cudaSuccess;
+    dim3 grid((p.x1 - p.x0 + PT_TILE_W - 1) / PT_TILE_W, owned), block(256);
     if (variant == 0) render_kernel<Cfg, 0><<<grid, block, 0, stream>>>(p);
     else if (variant == 1) render_kernel<Cfg, 1><<<grid, block, 0, stream>>>(p);
     else render_kernel<Cfg, 2><<<grid, block, 0, stream>>>(p);

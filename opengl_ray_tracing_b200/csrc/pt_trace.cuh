@@ -43,14 +43,15 @@ __device__ __forceinline__ float hit_aabb(const Ray& r, V3 AA, V3 BB, float& ent
 // hitTriangle, P:251-301, up to the hit decision.  N is the unit face normal normalize(cross(p2-p1,p3-p1))
 // BEFORE the reference's back-face flip: t and the inside test are invariant under N -> -N in IEEE
 // arithmetic (negation commutes exactly with *, + and /), so the flip only sets isInside.
-// `best` implements the strict closest-hit rule: a candidate must have t < best to matter.
+// `best` implements the strict closest-hit rule: a candidate must have t < best to matter (t == best also
+// qualifies when allow_tie is set — see trace_wide's early far-leaf test).
 __device__ __forceinline__ bool hit_triangle(const Ray& r, V3 p1, V3 p2, V3 p3, V3 N, float best, float& t_out,
-                                             bool& inside) {
+                                             bool& inside, bool allow_tie = false) {
     float Nd = s_dot(N, r.d);
     if (fabsf(Nd) < 0.00001f) return false;
     float t = s_div(s_sub(s_dot(N, p1), s_dot(r.o, N)), Nd);
     if (t < 0.0005f) return false;
-    if (!(t < best)) return false;
+    if (!(t < best) && !(allow_tie && t == best)) return false;
     V3 P = s_point(r.o, r.d, t);
     float s1 = s_dot(s_cross(s_sub3(p2, p1), s_sub3(P, p1)), N);
     float s2 = s_dot(s_cross(s_sub3(p3, p2), s_sub3(P, p2)), N);
@@ -110,70 +111,169 @@ static __device__ __noinline__ TraceResult trace_ref(const DevScene& sc, V3 orig
 // distance t of a triangle on the box face are different roundings of the same number, so a bare
 // `entry > best` could, in principle, cull the very triangle that defines best's successor.
 #define PT_CULL_SLACK 1.0000153f
-// Deferred-subtree stack capacity = the reference's own `int stack[256]` (P:340).  Local memory is
-// interleaved per lane, so only the slots a ray actually touches cost cache lines.
-#define PT_STACK 256
+// Deferred-subtree stack.  Only INNER nodes are ever deferred (see below), which keeps the need small even on
+// the reference builder's degenerate SAH chains (tree depth 6781 on the 1M-triangle scene; deepest stack seen
+// by the oracle's model of this traversal: 59).  Overflow is detected, flagged and reported as PT_ERANGE.
+#define PT_STACK 128
+
+struct WideState {
+    TraceResult res;
+    float cull;
+    int early_sp;                // >= 0: res came from a far leaf tested ahead of its turn at that stack depth
+    bool tie;                    // trace_fast only: two different triangles hit at exactly the same distance
+};
+
+// hitArray over one leaf.  `early`: this leaf is a FAR child being tested before the near subtree (its turn in
+// the reference's order comes later).  Exact-distance ties must still go to whoever the reference visits first:
+// an early hit needs strictly smaller t, and while an early hit is the best, in-turn candidates win ties.
+// TIE_DETECT (trace_fast, where the visiting order is not the reference's): an exact tie between two triangles is
+// not resolved here but reported, and the caller re-traces the ray on the reference topology.
+template <bool ANYHIT, bool TIE_DETECT>
+__device__ __forceinline__ bool wide_leaf(const DevScene& sc, const Ray& r, uint32_t ref, bool early, int sp, WideState& st) {
+    const uint32_t first = ref_index(ref), cnt = ref_count(ref);
+    for (uint32_t i = first; i < first + cnt; i++) {
+        const float4* g = sc.trigeo + 3 * (size_t)i;
+        float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2);
+        float tt; bool ins;
+        const bool allow_tie = TIE_DETECT ? (!ANYHIT && st.res.tri >= 0) : (!early && st.early_sp >= 0);
+        if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), mk3(a.w, b.w, c.w), st.res.t, tt, ins,
+                         allow_tie)) {
+            if (TIE_DETECT && !ANYHIT && tt == st.res.t) { st.tie = true; continue; }
+            st.res.t = tt; st.res.tri = (int)i; st.res.inside = ins;
+            if (ANYHIT) return true;
+            st.cull = s_mul(tt, PT_CULL_SLACK);
+            st.early_sp = early ? sp : -1;
+        }
+    }
+    return false;
+}
 
 template <bool ANYHIT, int STACK>
 __device__ __forceinline__ TraceResult trace_wide(const DevScene& sc, V3 origin, V3 dir) {
     Ray r = make_ray(origin, dir);
-    TraceResult res; res.tri = -1; res.t = PT_INF; res.inside = false;
-    float cull = PT_INF;
+    WideState st;
+    st.res.tri = -1; st.res.t = PT_INF; st.res.inside = false;
+    st.cull = PT_INF; st.early_sp = -1; st.tie = false;
     uint32_t stack_ref[STACK];
     float stack_t[STACK];
     int sp = 0;
     uint32_t ref = sc.root_ref;
+    if (ref_count(ref)) {                             // the whole scene is one leaf
+        wide_leaf<ANYHIT, false>(sc, r, ref, false, 0, st);
+        return st.res;
+    }
     while (true) {
-        if (ref_count(ref)) {
-            // leaf: triangles first .. first+count-1 in order (hitArray)
-            uint32_t first = ref_index(ref), cnt = ref_count(ref);
-            for (uint32_t i = first; i < first + cnt; i++) {
-                const float4* g = sc.trigeo + 3 * (size_t)i;
-                float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2);
-                float tt; bool ins;
-                if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), mk3(a.w, b.w, c.w),
-                                 res.t, tt, ins)) {
-                    res.t = tt; res.tri = (int)i; res.inside = ins;
-                    if (ANYHIT) return res;
-                    cull = s_mul(tt, PT_CULL_SLACK);
-                }
+        // ref is an inner node: one 64-byte record holds both child boxes and both child refs
+        const float4* w = sc.wnodes + 4 * (size_t)ref_index(ref);
+        float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
+        float e1, e2;
+        float d1 = hit_aabb(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), e1);
+        float d2 = hit_aabb(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), e2);
+        const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+        const bool h1 = d1 > 0.0f, h2 = d2 > 0.0f;    // the reference's "push" conditions (P:367-379)
+        uint32_t next = PT_REF_NONE;
+        if (h1 && h2) {
+            const bool left_first = d1 < d2;          // near child first (P:368)
+            const uint32_t nref = left_first ? lref : rref, fref = left_first ? rref : lref;
+            const float ne = left_first ? e1 : e2, fe = left_first ? e2 : e1;
+            const bool nleaf = ref_count(nref) != 0, fleaf = ref_count(fref) != 0;
+            if (nleaf) {
+                if (ne <= st.cull && wide_leaf<ANYHIT, false>(sc, r, nref, false, sp, st)) return st.res;
+                if (fleaf) { if (fe <= st.cull && wide_leaf<ANYHIT, false>(sc, r, fref, false, sp, st)) return st.res; }
+                else if (fe <= st.cull) next = fref;
+            } else if (fleaf) {
+                // far leaf, near subtree: test the leaf NOW rather than defer it
+                if (fe <= st.cull && wide_leaf<ANYHIT, false>(sc, r, fref, true, sp, st)) return st.res;
+                if (ne <= st.cull) next = nref;
+            } else {
+                const bool ng = ne <= st.cull, fg = fe <= st.cull;
+                if (ng && fg) {
+                    if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; break; }
+                    stack_ref[sp] = fref; stack_t[sp] = fe; sp++;
+                    next = nref;
+                } else if (ng) next = nref;
+                else if (fg) next = fref;
             }
-        } else {
-            const float4* w = sc.wnodes + 4 * (size_t)ref_index(ref);
-            float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
-            float e1, e2;
-            float d1 = hit_aabb(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), e1);
-            float d2 = hit_aabb(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), e2);
-            uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
-            bool h1 = (d1 > 0.0f) && (lref != PT_REF_NONE), h2 = (d2 > 0.0f) && (rref != PT_REF_NONE);
-            bool g1 = h1 && (e1 <= cull), g2 = h2 && (e2 <= cull);
-            if (h1 && h2) {
-                // near child first (P:367-374): left iff d1 < d2
-                bool left_first = d1 < d2;
-                uint32_t nref = left_first ? lref : rref, fref = left_first ? rref : lref;
-                float ne = left_first ? e1 : e2, fe = left_first ? e2 : e1;
-                bool ng = left_first ? g1 : g2, fg = left_first ? g2 : g1;
-                if (fg) {
-                    if (ng) {
-                        if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; break; }
-                        stack_ref[sp] = fref; stack_t[sp] = fe; sp++; ref = nref; continue;
-                    }
-                    ref = fref; continue;
-                }
-                if (ng) { ref = nref; continue; }
-                (void)ne;
-            } else if (g1) { ref = lref; continue; }
-            else if (g2) { ref = rref; continue; }
+        } else if (h1 || h2) {
+            const uint32_t cref = h1 ? lref : rref;
+            const float ce = h1 ? e1 : e2;
+            if (ce <= st.cull) {
+                if (ref_count(cref)) { if (wide_leaf<ANYHIT, false>(sc, r, cref, false, sp, st)) return st.res; }
+                else next = cref;
+            }
         }
-        // pop the next subtree still worth visiting
+        if (next != PT_REF_NONE) { ref = next; continue; }
+        // pop the next deferred subtree still worth visiting
         bool found = false;
         while (sp > 0) {
             sp--;
-            if (stack_t[sp] <= cull) { ref = stack_ref[sp]; found = true; break; }
+            if (st.early_sp > sp) st.early_sp = -1;   // the early leaf's own turn has passed: ties are strict again
+            if (stack_t[sp] <= st.cull) { ref = stack_ref[sp]; found = true; break; }
         }
         if (!found) break;
     }
-    return res;
+    return st.res;
+}
+
+// ---- the fast-topology traversal -------------------------------------------------------------------
+// Same node format, but over the binned-SAH tree of pt_build.cpp whose leaves are the reference's leaves.  A leaf
+// child's box in the parent IS the reference leaf's box, so `hit_aabb(...) > 0` on it is exactly the reference's
+// condition for visiting that leaf; inner boxes are unions of leaf boxes, hence conservative.  The visiting order
+// here is nearest-entry-first (not the reference's), which can only matter for an exact tie between two triangles:
+// that is detected (st.tie) and the ray is re-traced on the reference topology.
+template <bool ANYHIT, int STACK>
+__device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin, V3 dir) {
+    Ray r = make_ray(origin, dir);
+    WideState st;
+    st.res.tri = -1; st.res.t = PT_INF; st.res.inside = false;
+    st.cull = PT_INF; st.early_sp = -1; st.tie = false;
+    uint32_t stack_ref[STACK];
+    float stack_t[STACK];
+    int sp = 0;
+    uint32_t ref = sc.root_fast;
+    if (ref_count(ref)) {
+        wide_leaf<ANYHIT, true>(sc, r, ref, false, 0, st);
+        return st.res;
+    }
+    while (true) {
+        const float4* w = sc.wnodes_fast + 4 * (size_t)ref_index(ref);
+        float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
+        float e1, e2;
+        float d1 = hit_aabb(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), e1);
+        float d2 = hit_aabb(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), e2);
+        const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+        bool g1 = (d1 > 0.0f) && (e1 <= st.cull), g2 = (d2 > 0.0f) && (e2 <= st.cull);
+        // leaf children are tested on the spot
+        if (g1 && ref_count(lref)) { if (wide_leaf<ANYHIT, true>(sc, r, lref, false, sp, st)) return st.res; g1 = false; }
+        if (g2 && ref_count(rref)) {
+            if (e2 <= st.cull && wide_leaf<ANYHIT, true>(sc, r, rref, false, sp, st)) return st.res;
+            g2 = false;
+        }
+        g1 = g1 && (e1 <= st.cull);
+        g2 = g2 && (e2 <= st.cull);
+        if (g1 && g2) {
+            const bool left_first = e1 <= e2;
+            if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; break; }
+            stack_ref[sp] = left_first ? rref : lref; stack_t[sp] = left_first ? e2 : e1; sp++;
+            ref = left_first ? lref : rref;
+            continue;
+        }
+        if (g1) { ref = lref; continue; }
+        if (g2) { ref = rref; continue; }
+        bool found = false;
+        while (sp > 0) {
+            sp--;
+            if (stack_t[sp] <= st.cull) { ref = stack_ref[sp]; found = true; break; }
+        }
+        if (!found) break;
+    }
+    if (!ANYHIT && st.tie) st.res.tri = -2;           // caller: re-trace on the reference topology
+    return st.res;
+}
+
+// out-of-line so that the (practically never taken) tie path costs no registers in the hot loop
+static __device__ __noinline__ TraceResult trace_wide_fallback(const DevScene& sc, V3 origin, V3 dir) {
+    return trace_wide<false, PT_STACK>(sc, origin, dir);
 }
 
 // ---- what the shader's HitResult carries for the winning triangle (P:285-299) -------------------

@@ -17,10 +17,11 @@ _LIB_PATH = os.path.join(_HERE, "libpt.so")
 _lib = None
 
 LAMBERT, DISNEY_UNIFORM, DISNEY_IS_MIS = 0, 1, 2
-MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE = 0, 1, 2
+MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE, MODE_PARITY_FAST = 0, 1, 2, 3
 DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 
-EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_render_spp",
+ACC_MEAN, ACC_SUM = 0, 1
+EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_primary_ids", "pt_framebuffer_device_ptr", "pt_stream",
            "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_last_error",
            "pt_build_info"]
@@ -34,7 +35,8 @@ class PtConfig(C.Structure):
 class PtStats(C.Structure):
     _fields_ = [("rays", C.c_ulonglong), ("samples", C.c_ulonglong), ("render_ms", C.c_double),
                 ("launches", C.c_ulonglong), ("max_stack_depth", C.c_int), ("n_inner_nodes", C.c_int),
-                ("n_materials", C.c_int)]
+                ("n_materials", C.c_int), ("fast_tree_depth", C.c_int), ("n_fast_inner", C.c_int),
+                ("upload_build_ms", C.c_double)]
 
 
 class PtError(RuntimeError):
@@ -55,7 +57,9 @@ def lib():
         "pt_upload_scene": (C.c_int, [vp, f32p, C.c_int, f32p, C.c_int, f32p, f32p, C.c_int, C.c_int]),
         "pt_set_camera": (C.c_int, [vp, f32p, f32p]),
         "pt_set_region": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int]),
+        "pt_set_band_interleave": (C.c_int, [vp, C.c_int, C.c_int]),
         "pt_render_spp": (C.c_int, [vp, C.c_uint, C.c_uint]),
+        "pt_render_frames": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_int]),
         "pt_clear": (C.c_int, [vp]),
         "pt_readback": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_readback_primary_ids": (C.c_int, [vp, vp, C.c_size_t]),
@@ -122,9 +126,17 @@ class PathTracer:
     def set_region(self, x0, y0, x1, y1):
         _check(lib().pt_set_region(self._h, x0, y0, x1, y1), "pt_set_region")
 
+    def set_band_interleave(self, world, rank):
+        """This context renders 8-row band b iff b % world == rank (tile split in one launch)."""
+        _check(lib().pt_set_band_interleave(self._h, world, rank), "pt_set_band_interleave")
+
     def render_spp(self, first_frame, n_frames):
         """frameCounter = first_frame .. first_frame+n_frames-1; asynchronous."""
         _check(lib().pt_render_spp(self._h, first_frame, n_frames), "pt_render_spp")
+
+    def render_frames(self, first_frame, n_frames, stride=1, accumulate=ACC_MEAN):
+        """frameCounter = first_frame + k*stride; ACC_SUM adds colours instead of keeping the running mean."""
+        _check(lib().pt_render_frames(self._h, first_frame, n_frames, stride, accumulate), "pt_render_frames")
 
     def clear(self):
         _check(lib().pt_clear(self._h), "pt_clear")

@@ -56,6 +56,11 @@ def shader_to_cpp(src: str) -> str:
         src = re.sub(r"\.%s\b(?!\()" % sw, ".%s()" % sw, src)
     src = re.sub(r"\binout\s+(\w+)\s+", r"\1& ", src)            # inout T x -> T& x
     src = src.replace("const uint V[8*32] = {", "static constexpr uint V[8*32] = {")
+    # hitBVH's `int stack[256]` (pass1.fsh:340) is overrun by the reference's own SAH trees on large meshes (chains
+    # thousands of nodes deep); on a GPU that is undefined behaviour, on the CPU it would smash the C++ stack.
+    # The CPU build gets room for the deepest tree, so those scenes stay defined; nothing else changes.
+    assert src.count("int stack[256];") == 1
+    src = src.replace("int stack[256];", "int stack[16384];")
     # GLSL evaluates argument lists left to right; C++ leaves it open.  Two call sites have
     # side-effecting arguments (rand() twice): brace-initialisation is left-to-right in C++.
     aa_old = "vec2((rand()-0.5f)/float(width), (rand()-0.5f)/float(height))"

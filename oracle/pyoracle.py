@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 _f32p = C.POINTER(C.c_float)
 COUNTER_NAMES = ["rays", "ref_inner", "ref_leaf", "ref_tris", "ref_closer", "cull_inner", "cull_tris", "cull_hits",
-                 "max_sp", "overflow"]
+                 "max_sp", "over256", "texels", "wide_max_sp", "model_mismatch"]
 
 
 def build(force=False):
@@ -57,13 +57,13 @@ def render(variant, max_bounce, tris, nodes, hdr, hdrCache, width, height, eye, 
     if accum is None:
         accum = np.zeros((height, width, 4), np.float32)
     ids = np.full((height, width), -1, np.int32)
-    cnt = (C.c_ulonglong * 10)() if counters else None
+    cnt = (C.c_ulonglong * 13)() if counters else None
     x0, y0, x1, y1 = region if region else (0, 0, width, height)
     rc = lib().oracle_render(variant, max_bounce, math, _fp(tris), len(tris), _fp(nodes), len(nodes), _fp(hdr), _fp(hc),
                              hdr.shape[1], hdr.shape[0], width, height, _fp(eye), _fp(cam), C.c_uint(first_frame),
                              C.c_uint(n_frames), _fp(accum), ids.ctypes.data_as(C.POINTER(C.c_int)), cnt, x0, y0, x1, y1)
     if rc == -2:
-        raise OverflowError("oracle: a ray needed more than the reference's stack[256] (pass1.fsh:340)")
+        raise OverflowError("oracle: a ray needed more than 16384 traversal stack entries")
     if rc != 0:
         raise RuntimeError("oracle_render rejected its arguments")
     return accum, ids, (dict(zip(COUNTER_NAMES, [int(v) for v in cnt])) if counters else None)

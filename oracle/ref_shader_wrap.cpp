@@ -109,4 +109,25 @@ int ref_shader_render(const float* tris, int nTriangles, const float* nodes, int
     return 0;
 }
 
+/* Known-answer hooks: the shader's own rand() (pass1.fsh:73-89) and sobolVec2 / CranleyPattersonRotation
+   (pass1.fsh:112-136) evaluated for pixel (px,py) of a width x height target at frame `frame`. */
+static Fragment make_fragment(int px, int py, int width, int height, unsigned frame) {
+    Fragment::Uniforms u;
+    memset((void*)&u, 0, sizeof u);
+    u.frameCounter = frame; u.width = width; u.height = height;
+    return Fragment(u, vec3(ndc_of(px, width), ndc_of(py, height), 0.0f));
+}
+void ref_shader_rand_seq(int px, int py, int width, int height, unsigned frame, int n, float* out) {
+    Fragment f = make_fragment(px, py, width, height, frame);
+    for (int i = 0; i < n; i++) out[i] = f.rand();
+}
+#if REF_VARIANT == 2
+void ref_shader_sobol_cp(int px, int py, int width, int height, unsigned i, unsigned b, float* out4) {
+    Fragment f = make_fragment(px, py, width, height, 0);
+    vec2 s = f.sobolVec2(i, b);
+    vec2 r = f.CranleyPattersonRotation(s);
+    out4[0] = s.x; out4[1] = s.y; out4[2] = r.x; out4[3] = r.y;
+}
+#endif
+
 } /* extern "C" */
