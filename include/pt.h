@@ -119,6 +119,12 @@ int pt_readback(pt_ctx* ctx, float* rgba, size_t bytes);
 /* Parity hook: triangle index (into the uploaded array) of the primary hit of the LAST frame rendered, -1 = miss. */
 int pt_readback_primary_ids(pt_ctx* ctx, int* ids, size_t bytes);
 
+/* Profiling hook (no reference equivalent): when enabled, every render launch also writes, per pixel, the SM
+   cycles (clock64) its thread spent on that pixel in that launch — a cost heat map for finding stragglers.
+   Off by default; costs one pointer test per pixel when off. */
+int pt_enable_cost_map(pt_ctx* ctx, int on);
+int pt_readback_cost_map(pt_ctx* ctx, unsigned* cycles, size_t bytes);   /* W*H uint32, row 0 = bottom. Synchronises. */
+
 /* Multi-GPU plumbing: the device pointer of the framebuffer (W*H float4) and the context's cudaStream_t, so a
    host (torch.distributed / NCCL) can reduce or gather in place without a host round trip. */
 int pt_framebuffer_device_ptr(pt_ctx* ctx, void** dptr, size_t* bytes);

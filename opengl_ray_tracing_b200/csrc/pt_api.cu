@@ -48,6 +48,7 @@ struct pt_ctx {
     int* primary_ids = nullptr;
     unsigned long long* ray_counter = nullptr;
     int* error_flag = nullptr;
+    unsigned* cost = nullptr;    // cost map, allocated by pt_enable_cost_map
     // scene
     bool has_scene = false;
     int fast_depth = 0, n_fast_inner = 0;
@@ -235,7 +236,7 @@ int pt_destroy(pt_ctx* c) {
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
+    cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -440,7 +441,7 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
     p.band_world = c->band_world; p.band_rank = c->band_rank;
     p.first_frame = first_frame; p.n_frames = n_frames; p.frame_stride = stride; p.accumulate_sum = accumulate;
     p.max_bounce = c->cfg.max_bounce;
-    p.accum = c->accum; p.primary_ids = c->primary_ids; p.ray_counter = c->ray_counter;
+    p.accum = c->accum; p.primary_ids = c->primary_ids; p.ray_counter = c->ray_counter; p.cost = c->cost;
     CK(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e = c->cfg.mode == PT_MODE_FAST ? pt::launch_fast(p, c->cfg.variant, c->stream)
                                                  : pt::launch_parity(p, c->cfg.variant, c->cfg.mode, c->stream);
@@ -482,6 +483,32 @@ int pt_readback_primary_ids(pt_ctx* c, int* ids, size_t bytes) {
     if (bytes < need) return fail(PT_EINVAL, "pt_readback_primary_ids: buffer too small");
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaMemcpyAsync(ids, c->primary_ids, need, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return collect_timing(c);
+}
+
+int pt_enable_cost_map(pt_ctx* c, int on) {
+    if (!c) return fail(PT_EINVAL, "pt_enable_cost_map: null context");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    if (on && !c->cost) {
+        size_t npx = (size_t)c->cfg.width * c->cfg.height;
+        CK(cudaMalloc(&c->cost, npx * sizeof(unsigned)));
+        CK(cudaMemset(c->cost, 0, npx * sizeof(unsigned)));
+    } else if (!on && c->cost) {
+        cudaFree(c->cost);
+        c->cost = nullptr;
+    }
+    return PT_OK;
+}
+
+int pt_readback_cost_map(pt_ctx* c, unsigned* cycles, size_t bytes) {
+    if (!c || !cycles) return fail(PT_EINVAL, "pt_readback_cost_map: null argument");
+    if (!c->cost) return fail(PT_EINVAL, "pt_readback_cost_map: pt_enable_cost_map(ctx, 1) first");
+    size_t need = (size_t)c->cfg.width * c->cfg.height * sizeof(unsigned);
+    if (bytes < need) return fail(PT_EINVAL, "pt_readback_cost_map: buffer too small");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(cycles, c->cost, need, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return collect_timing(c);
 }

@@ -101,6 +101,7 @@ struct RenderParams {
     float4* accum;              // W*H float4, row 0 = bottom
     int* primary_ids;           // W*H
     unsigned long long* ray_counter;
+    unsigned* cost;             // optional W*H cost map (SM cycles spent on the pixel by the last launch) or null
 };
 
 struct Material {               // P:41-56 without the two fields no shader reads (IOR, transmission)

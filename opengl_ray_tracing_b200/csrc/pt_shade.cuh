@@ -420,6 +420,7 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
         const size_t idx = (size_t)py * p.width + px;
         float4 acc = p.accum[idx];
         int primary = -1;
+        const long long t_start = p.cost ? clock64() : 0;
         for (uint32_t f = 0; f < p.n_frames; f++) {
             const uint32_t frame = p.first_frame + f * p.frame_stride;
             V3 c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays);
@@ -437,6 +438,7 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
         acc.w = 1.0f;
         p.accum[idx] = acc;
         if (p.primary_ids) p.primary_ids[idx] = primary;
+        if (p.cost) p.cost[idx] = (unsigned)(clock64() - t_start);
     }
     // one atomic per warp for the ray counter
     for (int o = 16; o > 0; o >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o);

@@ -22,7 +22,7 @@ DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 
 ACC_MEAN, ACC_SUM = 0, 1
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_render_spp", "pt_render_frames",
-           "pt_clear", "pt_readback", "pt_readback_primary_ids", "pt_framebuffer_device_ptr", "pt_stream",
+           "pt_clear", "pt_readback", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
            "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_last_error",
            "pt_build_info"]
 
@@ -63,6 +63,8 @@ def lib():
         "pt_clear": (C.c_int, [vp]),
         "pt_readback": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_readback_primary_ids": (C.c_int, [vp, vp, C.c_size_t]),
+        "pt_enable_cost_map": (C.c_int, [vp, C.c_int]),
+        "pt_readback_cost_map": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_framebuffer_device_ptr": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
         "pt_stream": (C.c_int, [vp, C.POINTER(vp)]),
         "pt_scale_framebuffer": (C.c_int, [vp, C.c_float]),
@@ -157,6 +159,15 @@ class PathTracer:
     def readback_primary_ids(self) -> np.ndarray:
         out = np.empty((self.height, self.width), np.int32)
         _check(lib().pt_readback_primary_ids(self._h, out.ctypes.data, out.nbytes), "pt_readback_primary_ids")
+        return out
+
+    def enable_cost_map(self, on=True):
+        _check(lib().pt_enable_cost_map(self._h, int(on)), "pt_enable_cost_map")
+
+    def readback_cost_map(self) -> np.ndarray:
+        """uint32 [H, W]: SM cycles each pixel's thread spent in the last launch."""
+        out = np.empty((self.height, self.width), np.uint32)
+        _check(lib().pt_readback_cost_map(self._h, out.ctypes.data, out.nbytes), "pt_readback_cost_map")
         return out
 
     def framebuffer_device_ptr(self):
