@@ -49,12 +49,22 @@ extern "C" {
                                      arithmetic: bit-identical to the oracle too — proves that neither the layout nor
                                      the topology change any result */
 
+#define PT_MODE_FAST_COUNT    4   /* PT_MODE_FAST with traversal work counters compiled in (PtStats.inner_visits …): the
+                                     source of the roofline's algorithmic bytes; slower, never the timed path */
+
+/* how a sample is scheduled on the GPU (same arithmetic, same results) */
+#define PT_PIPELINE_MEGAKERNEL 0  /* one thread per pixel runs the whole path (ray generation .. accumulation) */
+#define PT_PIPELINE_WAVEFRONT  1  /* generate / shade / shadow / extend / accumulate kernels with compacted path queues
+                                     in HBM (DESIGN.md "Pipelines"); not available for PT_MODE_PARITY_REF */
+#define PT_PIPELINE_PERSISTENT 2  /* persistent warps claim (8x4 tile, frame) items frame-major and accumulate in frame order */
+
 typedef struct PtConfig {
     int variant;        /* PT_VARIANT_* */
     int width, height;  /* framebuffer size; pass1.width/height M:82-83, uniforms M:871-872 */
     int max_bounce;     /* <= 0: the variant's default (2 / 5 / 2); variant 2 supports <= 4 (8 Sobol dims, P:92) */
     int device;         /* CUDA device ordinal */
     int mode;           /* PT_MODE_* */
+    int pipeline;       /* PT_PIPELINE_* */
 } PtConfig;
 
 typedef struct PtStats {
@@ -68,6 +78,10 @@ typedef struct PtStats {
     int fast_tree_depth;              /* depth of the traversal topology built at upload (pt_build.cpp) */
     int n_fast_inner;                 /* its inner-node count */
     double upload_build_ms;           /* host time spent building that topology in the last pt_upload_scene */
+    unsigned long long inner_visits;  /* PT_MODE_FAST_COUNT only: inner nodes fetched since the last reset */
+    unsigned long long tri_tests;     /*   triangles tested */
+    unsigned long long leaf_candidates; /* triangle hits that went through the reference-leaf box test */
+    unsigned long long tie_retraces;  /*   rays re-traced on the reference topology because of an exact-distance tie */
 } PtStats;
 
 typedef struct pt_ctx pt_ctx;
@@ -135,6 +149,9 @@ int pt_scale_framebuffer(pt_ctx* ctx, float scale);
 int pt_synchronize(pt_ctx* ctx);
 int pt_get_stats(pt_ctx* ctx, PtStats* out);
 int pt_reset_stats(pt_ctx* ctx);
+/* PT_MODE_FAST_COUNT: log2 histogram of traversal steps (inner nodes + triangles) per ray since the last reset;
+   bucket k counts rays with 2^(k-1) <= steps < 2^k (bucket 0: no step).  n >= 33. */
+int pt_get_ray_histogram(pt_ctx* ctx, unsigned long long* buckets, int n);
 
 const char* pt_last_error(void);
 /* "sm_100a" build tag + whether a CUDA device is visible; never fails (used by the CPU-only symbol test) */

@@ -25,9 +25,16 @@
 
 namespace pt {
 cudaError_t launch_parity(const RenderParams& p, int variant, int which, cudaStream_t stream);
-struct FastTree { std::vector<float> wnodes; uint32_t root_ref = 0; int depth = 0; int n_leaves = 0; };
-void build_fast_tree(const float* nodes_raw, int nNodes, FastTree& out, int threads);
-cudaError_t launch_fast(const RenderParams& p, int variant, cudaStream_t stream);
+struct FastTree {
+    std::vector<float> wnodes; std::vector<int> order, leaf_node;
+    uint32_t root_ref = 0; int depth = 0; int n_leaves = 0; float pad = 0.0f;
+};
+void build_fast_tree(const float* tris_raw, int nTriangles, const float* nodes_raw, int nNodes, FastTree& out, int threads);
+cudaError_t launch_fast(const RenderParams& p, int variant, bool count, cudaStream_t stream);
+cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
+cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
+cudaError_t launch_persistent_parity(const RenderParams& p, int variant, int which, int grid, cudaStream_t stream);
+cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int which, int grid, cudaStream_t stream);
 }
 
 static thread_local std::string g_err;
@@ -49,12 +56,17 @@ struct pt_ctx {
     unsigned long long* ray_counter = nullptr;
     int* error_flag = nullptr;
     unsigned* cost = nullptr;    // cost map, allocated by pt_enable_cost_map
+    pt::WaveBuffers wf;          // wavefront path state, allocated at the first wavefront render
+    void* wf_block = nullptr;
+    uint32_t* sched = nullptr;   // persistent pipeline: work head + per-tile progress
+    int num_sms = 0;
     // scene
     bool has_scene = false;
     int fast_depth = 0, n_fast_inner = 0;
     double build_ms = 0.0;
     float *tris_raw = nullptr, *nodes_raw = nullptr;
-    float4 *wnodes = nullptr, *wnodes_fast = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr;
+    float4 *wnodes = nullptr, *wnodes_fast = nullptr, *trigeo_fast = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr;
+    int2* trimeta = nullptr;
     pt::DevScene sc;
     // camera + region
     float eye[3] = {0, 0, 4};
@@ -117,6 +129,18 @@ __global__ void k_build_tris(const float* __restrict__ tris, int nTriangles, con
     shade[3 * (size_t)i + 2] = make_float4(t[15], t[16], t[17], 0.f);
 }
 
+// trigeo in the traversal tree's order + (uploaded index, reference leaf node) per re-ordered triangle
+__global__ void k_gather_tris(const float4* __restrict__ geo, const int* __restrict__ order, const int* __restrict__ leaf_node,
+                              int nTriangles, float4* __restrict__ geo_fast, int2* __restrict__ meta) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nTriangles) return;
+    const int o = order[i];
+    geo_fast[3 * (size_t)i] = geo[3 * (size_t)o];
+    geo_fast[3 * (size_t)i + 1] = geo[3 * (size_t)o + 1];
+    geo_fast[3 * (size_t)i + 2] = geo[3 * (size_t)o + 2];
+    meta[i] = make_int2(o, leaf_node[i]);
+}
+
 __global__ void k_rgb_to_float4(const float* __restrict__ src, size_t n, float4* __restrict__ dst) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -144,6 +168,8 @@ struct MatHash {
 };
 
 void free_scene(pt_ctx* c) {
+    cudaFree(c->trigeo_fast); cudaFree(c->trimeta);
+    c->trigeo_fast = nullptr; c->trimeta = nullptr;
     cudaFree(c->tris_raw); cudaFree(c->nodes_raw); cudaFree(c->wnodes); cudaFree(c->wnodes_fast); cudaFree(c->trigeo); cudaFree(c->trishade);
     cudaFree(c->materials); cudaFree(c->hdr4); cudaFree(c->cache4);
     c->tris_raw = c->nodes_raw = nullptr;
@@ -175,6 +201,34 @@ int validate_tree(const float* nodes, int nNodes, int nTriangles, std::string& w
     return max_depth;
 }
 
+// One device allocation carved into the wavefront's struct-of-arrays (DESIGN.md "HBM layout").
+int alloc_wavefront(pt_ctx* c) {
+    if (c->wf_block) return PT_OK;
+    const size_t np = (size_t)c->cfg.width * c->cfg.height;
+    const int mb = c->cfg.max_bounce;
+    const size_t nslots = c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS ? 1 + 2 * (size_t)mb : 1 + (size_t)mb;
+    const size_t ctr_bytes = (size_t)2 * (3 * PT_WF_MAX_BOUNCE + 2) * 64 * sizeof(uint32_t);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t o_ro = take(np * 16), o_rd = take(np * 16), o_hist = take(np * 16), o_fr = take(np * 16), o_sh = take(np * 16);
+    const size_t o_hit = take(np * 8), o_seed = take(np * 4), o_nb = take(np * 4), o_terms = take(np * 16 * nslots);
+    const size_t o_q0 = take(np * 4), o_q1 = take(np * 4), o_q2 = take(np * 4), o_qs = take(np * 4), o_qe = take(np * 4);
+    const size_t o_ctr = take(ctr_bytes);
+    cudaError_t e = cudaMalloc(&c->wf_block, off);
+    if (e != cudaSuccess) { c->wf_block = nullptr; return fail(PT_ECUDA, std::string("wavefront path state: ") + cudaGetErrorString(e)); }
+    char* b = (char*)c->wf_block;
+    pt::WaveBuffers& w = c->wf;
+    w.ray_o = (float4*)(b + o_ro); w.ray_d = (float4*)(b + o_rd); w.hist = (float4*)(b + o_hist); w.fr = (float4*)(b + o_fr);
+    w.sh_d = (float4*)(b + o_sh); w.hit = (int2*)(b + o_hit); w.seed = (uint32_t*)(b + o_seed); w.nb = (int*)(b + o_nb);
+    w.terms = (float4*)(b + o_terms);
+    w.q_shade[0] = (uint32_t*)(b + o_q0);
+    for (int k = 1; k <= PT_WF_MAX_BOUNCE; k++) w.q_shade[k] = (uint32_t*)(b + ((k & 1) ? o_q1 : o_q2));   // consumed before re-filled
+    w.q_shadow = (uint32_t*)(b + o_qs); w.q_extend = (uint32_t*)(b + o_qe);
+    w.counters = (uint32_t*)(b + o_ctr);
+    w.npaths = np;
+    return PT_OK;
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
@@ -196,12 +250,18 @@ const char* pt_build_info(void) {
 int pt_create(const PtConfig* cfg, pt_ctx** out) {
     if (!cfg || !out) return fail(PT_EINVAL, "pt_create: null argument");
     if (cfg->variant < 0 || cfg->variant > 2) return fail(PT_EINVAL, "pt_create: variant must be 0, 1 or 2");
-    if (cfg->mode < 0 || cfg->mode > 3) return fail(PT_EINVAL, "pt_create: mode must be one of PT_MODE_*");
+    if (cfg->mode < 0 || cfg->mode > 4) return fail(PT_EINVAL, "pt_create: mode must be one of PT_MODE_*");
     if (cfg->width <= 0 || cfg->height <= 0 || cfg->width > 16384 || cfg->height > 16384)
         return fail(PT_EINVAL, "pt_create: width/height out of range");
     int mb = cfg->max_bounce > 0 ? cfg->max_bounce : (cfg->variant == PT_VARIANT_DISNEY_UNIFORM ? 5 : 2);
     if (cfg->variant == PT_VARIANT_DISNEY_IS_MIS && mb > 4)
         return fail(PT_EINVAL, "pt_create: variant 2 supports max_bounce <= 4 (8 Sobol dimensions, pass1.fsh:92)");
+    if (cfg->pipeline < PT_PIPELINE_MEGAKERNEL || cfg->pipeline > PT_PIPELINE_PERSISTENT)
+        return fail(PT_EINVAL, "pt_create: pipeline must be one of PT_PIPELINE_*");
+    if (cfg->pipeline == PT_PIPELINE_WAVEFRONT && cfg->mode == PT_MODE_PARITY_REF)
+        return fail(PT_EINVAL, "pt_create: PT_MODE_PARITY_REF (the reference's own layout and traversal) runs as a megakernel only");
+    if (cfg->pipeline == PT_PIPELINE_WAVEFRONT && mb > PT_WF_MAX_BOUNCE)
+        return fail(PT_EINVAL, "pt_create: the wavefront pipeline supports max_bounce <= 8");
     int ndev = 0;
     CK(cudaGetDeviceCount(&ndev));
     if (cfg->device < 0 || cfg->device >= ndev) return fail(PT_EINVAL, "pt_create: no such CUDA device");
@@ -212,18 +272,20 @@ int pt_create(const PtConfig* cfg, pt_ctx** out) {
     c->cfg.max_bounce = mb;
     c->x1 = cfg->width; c->y1 = cfg->height;
     std::memset(&c->sc, 0, sizeof c->sc);
+    std::memset(&c->wf, 0, sizeof c->wf);
+    cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, cfg->device);
     size_t npx = (size_t)cfg->width * cfg->height;
     cudaError_t e;
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
         (e = cudaMalloc(&c->accum, npx * sizeof(float4))) != cudaSuccess ||
         (e = cudaMalloc(&c->primary_ids, npx * sizeof(int))) != cudaSuccess ||
-        (e = cudaMalloc(&c->ray_counter, sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMalloc(&c->ray_counter, 48 * sizeof(unsigned long long))) != cudaSuccess ||
         (e = cudaMalloc(&c->error_flag, sizeof(int))) != cudaSuccess ||
         (e = cudaMemsetAsync(c->error_flag, 0, sizeof(int), c->stream)) != cudaSuccess ||
         (e = cudaMemsetAsync(c->accum, 0, npx * sizeof(float4), c->stream)) != cudaSuccess ||
         (e = cudaMemsetAsync(c->primary_ids, 0xff, npx * sizeof(int), c->stream)) != cudaSuccess ||
-        (e = cudaMemsetAsync(c->ray_counter, 0, sizeof(unsigned long long), c->stream)) != cudaSuccess) {
+        (e = cudaMemsetAsync(c->ray_counter, 0, 48 * sizeof(unsigned long long), c->stream)) != cudaSuccess) {
         pt_destroy(c);
         return fail(PT_ECUDA, std::string("pt_create: ") + cudaGetErrorString(e));
     }
@@ -236,7 +298,7 @@ int pt_destroy(pt_ctx* c) {
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
+    cudaFree(c->wf_block); cudaFree(c->sched); cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -288,7 +350,7 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     free_scene(c);
     cudaStream_t st = c->stream;
     const size_t ntex = (size_t)hdrW * hdrH;
-    int *d_flag = nullptr, *d_widx = nullptr, *d_matid = nullptr;
+    int *d_flag = nullptr, *d_widx = nullptr, *d_matid = nullptr, *d_order = nullptr, *d_leaf = nullptr;
     float* d_tmp = nullptr;
     void* d_scan = nullptr;
     size_t scan_bytes = 0;
@@ -324,19 +386,6 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         k_build_wide<<<(nNodes + 255) / 256, 256, 0, st>>>(c->nodes_raw, nNodes, d_flag, d_widx, c->wnodes);
         CKU(cudaGetLastError());
     }
-    // traversal topology: binned SAH over the reference's leaves (host build, pt_build.cpp)
-    {
-        pt::FastTree ft;
-        int hw = (int)std::thread::hardware_concurrency();
-        auto t0 = std::chrono::steady_clock::now();
-        pt::build_fast_tree(nodes, nNodes, ft, hw > 0 ? (hw > 32 ? 32 : hw) : 1);
-        c->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-        root_fast = ft.root_ref; fast_depth = ft.depth; nFastInner = (int)(ft.wnodes.size() / 16);
-        CKU(cudaMalloc(&c->wnodes_fast, (ft.wnodes.empty() ? 16 : ft.wnodes.size()) * sizeof(float)));
-        if (!ft.wnodes.empty())
-            CKU(cudaMemcpyAsync(c->wnodes_fast, ft.wnodes.data(), ft.wnodes.size() * sizeof(float), cudaMemcpyHostToDevice, st));
-        CKU(cudaStreamSynchronize(st));               // ft goes out of scope
-    }
     // triangles
     CKU(cudaMalloc(&d_matid, (size_t)nTriangles * sizeof(int)));
     CKU(cudaMemcpyAsync(d_matid, mat_id.data(), (size_t)nTriangles * sizeof(int), cudaMemcpyHostToDevice, st));
@@ -344,6 +393,28 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     CKU(cudaMalloc(&c->trishade, (size_t)nTriangles * 3 * sizeof(float4)));
     k_build_tris<<<(nTriangles + 255) / 256, 256, 0, st>>>(c->tris_raw, nTriangles, d_matid, c->trigeo, c->trishade);
     CKU(cudaGetLastError());
+    // traversal topology: binned SAH over the triangles (host build, pt_build.cpp), then gather trigeo into its order
+    {
+        pt::FastTree ft;
+        int hw = (int)std::thread::hardware_concurrency();
+        auto t0 = std::chrono::steady_clock::now();
+        pt::build_fast_tree(tris, nTriangles, nodes, nNodes, ft, hw > 0 ? (hw > 32 ? 32 : hw) : 1);
+        c->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        root_fast = ft.root_ref; fast_depth = ft.depth; nFastInner = (int)(ft.wnodes.size() / 16);
+        if (nFastInner >= (1 << 24)) { rc = fail(PT_ERANGE, "pt_upload_scene: traversal tree has >= 2^24 inner nodes"); goto done; }
+        CKU(cudaMalloc(&c->wnodes_fast, (ft.wnodes.empty() ? 16 : ft.wnodes.size()) * sizeof(float)));
+        if (!ft.wnodes.empty())
+            CKU(cudaMemcpyAsync(c->wnodes_fast, ft.wnodes.data(), ft.wnodes.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+        CKU(cudaMalloc(&d_order, (size_t)nTriangles * sizeof(int)));
+        CKU(cudaMalloc(&d_leaf, (size_t)nTriangles * sizeof(int)));
+        CKU(cudaMemcpyAsync(d_order, ft.order.data(), (size_t)nTriangles * sizeof(int), cudaMemcpyHostToDevice, st));
+        CKU(cudaMemcpyAsync(d_leaf, ft.leaf_node.data(), (size_t)nTriangles * sizeof(int), cudaMemcpyHostToDevice, st));
+        CKU(cudaMalloc(&c->trigeo_fast, (size_t)nTriangles * 3 * sizeof(float4)));
+        CKU(cudaMalloc(&c->trimeta, (size_t)nTriangles * sizeof(int2)));
+        k_gather_tris<<<(nTriangles + 255) / 256, 256, 0, st>>>(c->trigeo, d_order, d_leaf, nTriangles, c->trigeo_fast, c->trimeta);
+        CKU(cudaGetLastError());
+        CKU(cudaStreamSynchronize(st));               // ft goes out of scope
+    }
     CKU(cudaMalloc(&c->materials, (size_t)nMaterials * 4 * sizeof(float4)));
     CKU(cudaMemcpyAsync(c->materials, mat_table.data(), (size_t)nMaterials * 16 * sizeof(float), cudaMemcpyHostToDevice, st));
     // environment
@@ -363,17 +434,19 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     {
         pt::DevScene& s = c->sc;
         s.tris_raw = c->tris_raw; s.nodes_raw = c->nodes_raw; s.wnodes = c->wnodes; s.wnodes_fast = c->wnodes_fast; s.trigeo = c->trigeo;
+        s.trigeo_fast = c->trigeo_fast; s.trimeta = c->trimeta;
         s.root_fast = root_fast; c->fast_depth = fast_depth; c->n_fast_inner = nFastInner;
         s.trishade = c->trishade; s.materials = c->materials; s.hdr4 = c->hdr4; s.cache4 = c->cache4;
         s.nTriangles = nTriangles; s.nNodes = nNodes; s.nInner = nInner; s.nMaterials = nMaterials;
-        s.hdrW = hdrW; s.hdrH = hdrH; s.stack_depth = depth; s.error_flag = c->error_flag;
+        s.hdrW = hdrW; s.hdrH = hdrH; s.stack_depth = depth; s.error_flag = c->error_flag; s.ray_histogram = c->ray_counter + 8;
         // root = node 1: a leaf when the whole scene fits one leaf, else wide node 0
         int rn = (int)nodes[12 + 3], rindex = (int)nodes[12 + 4];
         s.root_ref = rn > 0 ? pt::ref_pack((uint32_t)rindex, (uint32_t)rn) : pt::ref_pack(0u, 0u);
         c->has_scene = true;
-        c->launches += 4 + (hdrCache ? 1 : 0);
+        c->launches += 5 + (hdrCache ? 1 : 0);
     }
 done:
+    cudaFree(d_order); cudaFree(d_leaf);
     cudaFree(d_flag); cudaFree(d_widx); cudaFree(d_matid); cudaFree(d_tmp); cudaFree(d_scan);
     if (rc != PT_OK) free_scene(c);
     return rc;
@@ -441,14 +514,46 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
     p.band_world = c->band_world; p.band_rank = c->band_rank;
     p.first_frame = first_frame; p.n_frames = n_frames; p.frame_stride = stride; p.accumulate_sum = accumulate;
     p.max_bounce = c->cfg.max_bounce;
-    p.accum = c->accum; p.primary_ids = c->primary_ids; p.ray_counter = c->ray_counter; p.cost = c->cost;
+    p.accum = c->accum; p.primary_ids = c->primary_ids; p.ray_counter = c->ray_counter; p.work_counters = c->ray_counter + 1; p.cost = c->cost;
+    const bool fastmode = c->cfg.mode == PT_MODE_FAST || c->cfg.mode == PT_MODE_FAST_COUNT;
+    const bool wavefront = c->cfg.pipeline == PT_PIPELINE_WAVEFRONT;
+    if (wavefront) {
+        rc = alloc_wavefront(c);
+        if (rc != PT_OK) return rc;
+        p.wf = c->wf;
+    } else {
+        std::memset(&p.wf, 0, sizeof p.wf);
+    }
+    const bool persistent = c->cfg.pipeline == PT_PIPELINE_PERSISTENT;
+    if (persistent && !c->sched) {
+        const size_t ntiles = (size_t)((c->cfg.width + 7) / 8) * (size_t)((c->cfg.height + 7) / 8) * 2;
+        CK(cudaMalloc(&c->sched, (64 + ntiles) * sizeof(uint32_t)));
+    }
+    p.sched = c->sched;
     CK(cudaEventRecord(c->ev0, c->stream));
-    cudaError_t e = c->cfg.mode == PT_MODE_FAST ? pt::launch_fast(p, c->cfg.variant, c->stream)
-                                                 : pt::launch_parity(p, c->cfg.variant, c->cfg.mode, c->stream);
+    cudaError_t e;
+    if (wavefront) {
+        const int grid = (c->num_sms > 0 ? c->num_sms : 148) * 8;
+        e = fastmode ? pt::launch_wavefront_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
+                     : pt::launch_wavefront_parity(p, c->cfg.variant, c->cfg.mode, grid, c->stream);
+    } else if (persistent) {
+        // registers allow 2-3 CTAs of 256 threads per SM; surplus CTAs find the work list empty and leave
+        const int grid = (c->num_sms > 0 ? c->num_sms : 148) * 3;
+        e = fastmode ? pt::launch_persistent_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
+                     : pt::launch_persistent_parity(p, c->cfg.variant, c->cfg.mode, grid, c->stream);
+    } else {
+        e = fastmode ? pt::launch_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, c->stream)
+                     : pt::launch_parity(p, c->cfg.variant, c->cfg.mode, c->stream);
+    }
     if (e != cudaSuccess) return fail(PT_ECUDA, std::string("render kernel launch: ") + cudaGetErrorString(e));
     CK(cudaEventRecord(c->ev1, c->stream));
     c->timing_pending = true;
-    c->launches += 1;
+    if (wavefront) {
+        const int mb = c->cfg.max_bounce;
+        c->launches += (unsigned long long)n_frames * (1 + (mb + 1) + mb * (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS ? 2 : 1) + 1);
+    } else {
+        c->launches += 1;
+    }
     {
         unsigned long long rows = 0;
         for (int y = c->y0, b = 0; y < c->y1; y += 8, b++)
@@ -549,13 +654,21 @@ int pt_get_stats(pt_ctx* c, PtStats* out) {
     CK(cudaStreamSynchronize(c->stream));
     int rc = collect_timing(c);
     if (rc != PT_OK) return rc;
-    unsigned long long rays = 0;
-    CK(cudaMemcpy(&rays, c->ray_counter, sizeof rays, cudaMemcpyDeviceToHost));
-    out->rays = rays; out->samples = c->samples; out->render_ms = c->render_ms; out->launches = c->launches;
+    unsigned long long cnt[5] = {0, 0, 0, 0, 0};
+    CK(cudaMemcpy(cnt, c->ray_counter, sizeof cnt, cudaMemcpyDeviceToHost));
+    out->rays = cnt[0]; out->inner_visits = cnt[1]; out->tri_tests = cnt[2]; out->leaf_candidates = cnt[3]; out->tie_retraces = cnt[4]; out->samples = c->samples; out->render_ms = c->render_ms; out->launches = c->launches;
     out->max_stack_depth = c->has_scene ? c->sc.stack_depth : 0;
     out->n_inner_nodes = c->has_scene ? c->sc.nInner : 0;
     out->n_materials = c->has_scene ? c->sc.nMaterials : 0;
     out->fast_tree_depth = c->fast_depth; out->n_fast_inner = c->n_fast_inner; out->upload_build_ms = c->build_ms;
+    return PT_OK;
+}
+
+int pt_get_ray_histogram(pt_ctx* c, unsigned long long* buckets, int n) {
+    if (!c || !buckets || n < 33) return fail(PT_EINVAL, "pt_get_ray_histogram: need room for 33 buckets");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaMemcpy(buckets, c->ray_counter + 8, 33 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     return PT_OK;
 }
 
@@ -565,7 +678,7 @@ int pt_reset_stats(pt_ctx* c) {
     CK(cudaStreamSynchronize(c->stream));
     int rc = collect_timing(c);
     if (rc != PT_OK) return rc;
-    CK(cudaMemset(c->ray_counter, 0, sizeof(unsigned long long)));
+    CK(cudaMemset(c->ray_counter, 0, 48 * sizeof(unsigned long long)));
     c->samples = 0; c->launches = 0; c->render_ms = 0.0;
     return PT_OK;
 }

@@ -74,7 +74,9 @@ struct DevScene {
     const float* nodes_raw;     // nNodes x 12 floats      (BVHNode_encoded)
     // traversal layout built on the device at upload
     const float4* wnodes;       // nInner x 4 float4 (64 B): child boxes + packed child refs, REFERENCE topology
-    const float4* wnodes_fast;  // same record format, binned-SAH topology over the reference's leaves (pt_build.cpp)
+    const float4* wnodes_fast;  // same record format, binned-SAH topology over the triangles (pt_build.cpp), padded boxes
+    const float4* trigeo_fast;  // trigeo re-ordered so that a leaf of wnodes_fast is a contiguous range
+    const int2* trimeta;        // per re-ordered triangle: (uploaded triangle index, reference leaf node holding it)
     const float4* trigeo;       // nTriangles x 3 float4 (48 B): (p1,N.x) (p2,N.y) (p3,N.z), N = unit face normal
     const float4* trishade;     // nTriangles x 3 float4 (48 B): (n1, matId) (n2, -) (n3, -)
     const float4* materials;    // nMaterials x 4 float4 (64 B)
@@ -84,9 +86,29 @@ struct DevScene {
     int hdrW, hdrH;
     uint32_t root_ref, root_fast;
     int stack_depth;            // depth of the tree = worst-case traversal stack
+    unsigned long long* ray_histogram;   // [33] log2 histogram of steps per ray (PT_MODE_FAST_COUNT)
     int* error_flag;            // set to PT_ERR_* by a kernel that had to give up (checked at the next sync)
 };
 #define PT_ERR_STACK 1          // traversal stack overflow (> 256 deferred subtrees; the reference's stack[256], P:340)
+
+// Path state of the wavefront pipeline (pt_wavefront.cuh): struct-of-arrays in HBM, indexed by pixel.
+#define PT_WF_MAX_BOUNCE 8
+struct WaveBuffers {
+    float4* ray_o;              // xyz = origin of the ray in flight (the hit point it leaves), w = its sampling pdf
+    float4* ray_d;              // xyz = direction, w = N.L of the sample that produced it
+    float4* hist;               // xyz = path throughput before this ray ("history", P:765)
+    float4* fr;                 // xyz = f_r of the sample that produced the ray
+    float4* sh_d;               // xyz = shadow-ray direction (origin = ray_o)
+    int2* hit;                  // x = triangle | inside << 31, y = bits of t
+    uint32_t* seed;             // wang-hash state carried across the stages
+    int* nb;                    // bounces whose term slots are valid when the path ended
+    float4* terms;              // [slot][path]: slot 0 = Le0, then per bounce (light term,) BRDF-ray term
+    uint32_t* q_shade[PT_WF_MAX_BOUNCE + 1];   // q_shade[0] (paths alive after the primary ray) also drives accumulate
+    uint32_t* q_shadow;
+    uint32_t* q_extend;
+    uint32_t* counters;         // queue tails and work-claim heads, one per 256 bytes
+    size_t npaths;              // = width * height
+};
 
 struct RenderParams {
     DevScene sc;
@@ -101,6 +123,9 @@ struct RenderParams {
     float4* accum;              // W*H float4, row 0 = bottom
     int* primary_ids;           // W*H
     unsigned long long* ray_counter;
+    unsigned long long* work_counters;   // [4]: inner nodes fetched, triangles tested, leaf-box candidates, - (PT_MODE_FAST_COUNT)
+    WaveBuffers wf;             // PT_PIPELINE_WAVEFRONT only
+    uint32_t* sched;            // PT_PIPELINE_PERSISTENT: [0] work head, [64 + tile] next frame allowed to accumulate
     unsigned* cost;             // optional W*H cost map (SM cycles spent on the pixel by the last launch) or null
 };
 

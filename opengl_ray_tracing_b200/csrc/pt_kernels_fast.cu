@@ -1,10 +1,19 @@
 // pt_kernels_fast.cu — the production configuration: FMA contraction on, SFU transcendental
 // approximations in shading.  Ray generation and all ray/box/triangle tests still use the strict
 // (un-fused, IEEE) helpers of pt_common.cuh, so the primary-hit triangle ids stay bit-exact.
-#include "pt_shade.cuh"
+#include "pt_wavefront.cuh"
 
 namespace pt {
-cudaError_t launch_fast(const RenderParams& p, int variant, cudaStream_t stream) {
+cudaError_t launch_fast(const RenderParams& p, int variant, bool count, cudaStream_t stream) {
+    if (count) return launch_render<CfgFastCount>(p, variant, stream);   // same arithmetic + traversal work counters
     return launch_render<CfgFast>(p, variant, stream);
+}
+cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream) {
+    if (count) return launch_persistent<CfgFastCount>(p, variant, grid, stream);
+    return launch_persistent<CfgFast>(p, variant, grid, stream);
+}
+cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream) {
+    if (count) return launch_wavefront<CfgFastCount>(p, variant, grid, stream);
+    return launch_wavefront<CfgFast>(p, variant, grid, stream);
 }
 }  // namespace pt

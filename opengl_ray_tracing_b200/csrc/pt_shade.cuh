@@ -42,17 +42,29 @@ struct MathFast {                 // SFU approximations where CUDA has them
     static __device__ __forceinline__ float log(float a) { return __logf(a); }
     static __device__ __forceinline__ float pow(float a, float b) { return __powf(a, b); }
 };
-struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; };
-struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; };
-struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  };
-struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  };
+struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; static const bool COUNT = false; };
+struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; };
+struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; };
+struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; };
+struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  };
+
+// counting configuration: histogram of traversal steps (inner nodes + triangles) per ray, log2 buckets
+__device__ __forceinline__ uint32_t ray_steps(const Counter<false>&) { return 0; }
+__device__ __forceinline__ uint32_t ray_steps(const Counter<true>& c) { return c.c.inner + c.c.tris; }
+__device__ __forceinline__ void note_ray(const Counter<false>&, uint32_t, unsigned long long*) {}
+__device__ __forceinline__ void note_ray(const Counter<true>& c, uint32_t before, unsigned long long* hist) {
+    const uint32_t n = c.c.inner + c.c.tris - before;
+    atomicAdd(hist + (n ? 32 - __clz(n) : 0), 1ull);
+}
 
 template <class Cfg, bool ANYHIT>
-__device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d) {
+__device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d, Counter<Cfg::COUNT>& cnt) {
     if (Cfg::RAW) return trace_ref(sc, o, d);
     if (Cfg::FAST_TREE) {
-        TraceResult tr = trace_fast<ANYHIT, PT_STACK>(sc, o, d);
-        if (!ANYHIT && tr.tri == -2) tr = trace_wide_fallback(sc, o, d);   // exact tie: let the reference order decide
+        const uint32_t steps0 = ray_steps(cnt);
+        TraceResult tr = trace_fast<ANYHIT, PT_STACK>(sc, o, d, cnt);
+        note_ray(cnt, steps0, sc.ray_histogram);
+        if (!ANYHIT && tr.tri == -2) { cnt.tie(); tr = trace_wide_fallback(sc, o, d); }   // exact tie: let the reference order decide
         return tr;
     }
     return trace_wide<ANYHIT, PT_STACK>(sc, o, d);
@@ -295,28 +307,33 @@ __device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 
     return reflect3(-V, H);
 }
 
-// ---- one sample of one pixel: main() of the three shaders ------------------------------------------
-// Returns this frame's colour BEFORE accumulation; primary_id = triangle of the primary hit (-1 miss).
-template <class Cfg, int VARIANT>
-__device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py, uint32_t frame, int& primary_id,
-                                           uint32_t& nrays) {
-    typedef typename Cfg::M M;
-    const DevScene& sc = p.sc;
-    uint32_t seed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + frame * 26699u) | 1u;            // P:73-76
-
-    // ray generation, P:846-850, in strict arithmetic (primary-hit ids must be bit-exact in every mode).
-    // pix = NDC of the fragment centre: ((k + 0.5) / n) * 2 - 1 (vshader.vsh:7-8 interpolated over the quad)
+// ray generation, P:846-850, in strict arithmetic (primary-hit ids must be bit-exact in every mode).
+// pix = NDC of the fragment centre: ((k + 0.5) / n) * 2 - 1 (vshader.vsh:7-8 interpolated over the quad)
+__device__ __forceinline__ void generate_ray(const RenderParams& p, int px, int py, uint32_t& seed, V3& o, V3& d) {
     float pixx = s_sub(s_mul(s_div(s_add((float)px, 0.5f), (float)p.width), 2.0f), 1.0f);
     float pixy = s_sub(s_mul(s_div(s_add((float)py, 0.5f), (float)p.height), 2.0f), 1.0f);
     float a1 = s_div(s_sub(rnd(seed), 0.5f), (float)p.width);
     float a2 = s_div(s_sub(rnd(seed), 0.5f), (float)p.height);
     float vx = s_add(pixx, a1), vy = s_add(pixy, a2), vz = -1.5f, vw = 0.0f;
     const float* m = p.cam;
-    V3 d = mk3(s_add(s_add(s_add(s_mul(m[0], vx), s_mul(m[4], vy)), s_mul(m[8], vz)), s_mul(m[12], vw)),
-               s_add(s_add(s_add(s_mul(m[1], vx), s_mul(m[5], vy)), s_mul(m[9], vz)), s_mul(m[13], vw)),
-               s_add(s_add(s_add(s_mul(m[2], vx), s_mul(m[6], vy)), s_mul(m[10], vz)), s_mul(m[14], vw)));
+    d = mk3(s_add(s_add(s_add(s_mul(m[0], vx), s_mul(m[4], vy)), s_mul(m[8], vz)), s_mul(m[12], vw)),
+            s_add(s_add(s_add(s_mul(m[1], vx), s_mul(m[5], vy)), s_mul(m[9], vz)), s_mul(m[13], vw)),
+            s_add(s_add(s_add(s_mul(m[2], vx), s_mul(m[6], vy)), s_mul(m[10], vz)), s_mul(m[14], vw)));
     d = s_normalize(d);
-    V3 o = mk3(p.eye[0], p.eye[1], p.eye[2]);
+    o = mk3(p.eye[0], p.eye[1], p.eye[2]);
+}
+
+// ---- one sample of one pixel: main() of the three shaders ------------------------------------------
+// Returns this frame's colour BEFORE accumulation; primary_id = triangle of the primary hit (-1 miss).
+template <class Cfg, int VARIANT>
+__device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py, uint32_t frame, int& primary_id,
+                                           uint32_t& nrays, Counter<Cfg::COUNT>& cnt) {
+    typedef typename Cfg::M M;
+    const DevScene& sc = p.sc;
+    uint32_t seed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + frame * 26699u) | 1u;            // P:73-76
+
+    V3 o, d;
+    generate_ray(p, px, py, seed, o, d);
 
     V3 Le0 = mk3(0, 0, 0), Lo = mk3(0, 0, 0), history = mk3(1, 1, 1);
     V3 f_r = mk3(0, 0, 0);
@@ -324,7 +341,7 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
     Material mat;
     int bounce = -1;                                  // -1: the ray in flight is the primary ray
     while (true) {
-        TraceResult tr = trace<Cfg, false>(sc, o, d);
+        TraceResult tr = trace<Cfg, false>(sc, o, d, cnt);
         nrays++;
         Hit hit;
         int mat_id;
@@ -362,7 +379,7 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
             float e2 = rnd(seed);
             V3 Ld = SampleHdr<M>(sc, e1, e2);
             if (dot(N, Ld) > 0.0f) {
-                TraceResult sh = trace<Cfg, true>(sc, hit.hitPoint, Ld);
+                TraceResult sh = trace<Cfg, true>(sc, hit.hitPoint, Ld, cnt);
                 nrays++;
                 if (sh.tri < 0) {
                     V3 color; float pdf_light;
@@ -406,6 +423,20 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
     return Le0 + Lo;
 }
 
+// adds a thread's traversal counters to the global ones (counting configuration only)
+__device__ __forceinline__ void flush_counts(Counter<false>&, unsigned long long*) {}
+__device__ __forceinline__ void flush_counts(Counter<true>& cnt, unsigned long long* out) {
+    uint32_t a = cnt.c.inner, b = cnt.c.tris, c = cnt.c.cand, d = cnt.c.ties;
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); c += __shfl_xor_sync(0xffffffffu, c, o);
+        d += __shfl_xor_sync(0xffffffffu, d, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(out, (unsigned long long)a); atomicAdd(out + 1, (unsigned long long)b); atomicAdd(out + 2, (unsigned long long)c);
+        if (d) atomicAdd(out + 3, (unsigned long long)d);
+    }
+}
+
 // ---- render kernel: one thread per pixel, a warp covers an 8x4 pixel tile, frames looped in registers ----
 #define PT_TILE_W 32     // CTA tile: 4 x 2 warps of 8 x 4 pixels
 #define PT_TILE_H 8
@@ -416,6 +447,7 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
     const int px = p.x0 + blockIdx.x * PT_TILE_W + (warp & 3) * 8 + (lane & 7);
     const int py = p.y0 + (blockIdx.y * p.band_world + p.band_rank) * PT_TILE_H + (warp >> 2) * 4 + (lane >> 3);
     uint32_t nrays = 0;
+    Counter<Cfg::COUNT> cnt;
     if (px < p.x1 && py < p.y1) {
         const size_t idx = (size_t)py * p.width + px;
         float4 acc = p.accum[idx];
@@ -423,7 +455,7 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
         const long long t_start = p.cost ? clock64() : 0;
         for (uint32_t f = 0; f < p.n_frames; f++) {
             const uint32_t frame = p.first_frame + f * p.frame_stride;
-            V3 c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays);
+            V3 c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays, cnt);
             if (p.accumulate_sum) {
                 acc.x = s_add(acc.x, c.x); acc.y = s_add(acc.y, c.y); acc.z = s_add(acc.z, c.z);
             } else {
@@ -443,6 +475,98 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
     // one atomic per warp for the ray counter
     for (int o = 16; o > 0; o >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o);
     if (lane == 0 && nrays) atomicAdd(p.ray_counter, (unsigned long long)nrays);
+    flush_counts(cnt, p.work_counters);
+}
+
+// ---- persistent render kernel: (8x4 pixel tile, frame) work items, frame-major, claimed dynamically ----------
+// The one-thread-per-pixel kernel above runs the n_frames of a pixel back to back in one thread, so a launch lasts
+// at least as long as its most expensive pixel times n_frames (on is-1M: a mesh tile = 3.6 ms of a 6.1 ms launch,
+// SMs 69 % busy, profiles/r01_megakernel_v2.md).  Here a resident warp repeatedly claims the next (tile, frame)
+// item, computes that one sample for its 32 pixels, and folds it into the framebuffer IN FRAME ORDER: progress[tile]
+// is the next frame allowed to accumulate; a warp that finishes frame f early waits for f-1 (which was claimed
+// before it, hence is running or done: no deadlock).  The running mean therefore sees the same sequence of
+// operations as the reference's ping-pong (P:868-869) and results stay bit-identical.
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <class Cfg, int VARIANT>
+__global__ void __launch_bounds__(256) render_persistent(const __grid_constant__ RenderParams p) {
+    const int lane = threadIdx.x & 31;
+    const int tiles_x = (p.x1 - p.x0 + 7) >> 3;
+    const int bands = (p.y1 - p.y0 + 7) >> 3;
+    const int owned = bands > p.band_rank ? (bands - p.band_rank + p.band_world - 1) / p.band_world : 0;
+    const uint32_t ntiles = (uint32_t)tiles_x * (uint32_t)owned * 2u;
+    const uint32_t nitems = ntiles * p.n_frames;
+    uint32_t* head = p.sched;                          // [0] = next item; progress starts 64 words in
+    uint32_t* progress = p.sched + 64;
+    uint32_t nrays = 0;
+    Counter<Cfg::COUNT> cnt;
+    for (;;) {
+        uint32_t item = 0;
+        if (lane == 0) item = atomicAdd(head, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= nitems) break;
+        const uint32_t f = item / ntiles, tile = item - f * ntiles;
+        const uint32_t strip = tile / (uint32_t)tiles_x, tx = tile - strip * (uint32_t)tiles_x;
+        const int px = p.x0 + (int)tx * 8 + (lane & 7);
+        const int py = p.y0 + ((int)(strip >> 1) * p.band_world + p.band_rank) * 8 + (int)(strip & 1u) * 4 + (lane >> 3);
+        const bool valid = px < p.x1 && py < p.y1;
+        const uint32_t frame = p.first_frame + f * p.frame_stride;
+        const long long t_start = p.cost ? clock64() : 0;
+        V3 c = mk3(0, 0, 0);
+        int primary = -1;
+        if (valid) c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays, cnt);
+        // ordered accumulation
+        if (lane == 0) while (ld_acquire_u32(progress + tile) != f) __nanosleep(32);
+        __syncwarp();
+        if (valid) {
+            const size_t idx = (size_t)py * p.width + px;
+            float4 acc = __ldcg(p.accum + idx);        // L2: another SM wrote the previous frame
+            if (p.accumulate_sum) {
+                acc.x = s_add(acc.x, c.x); acc.y = s_add(acc.y, c.y); acc.z = s_add(acc.z, c.z);
+            } else {
+                float a = s_div(1.0f, (float)(frame + 1u));
+                float b = s_sub(1.0f, a);
+                acc.x = s_add(s_mul(acc.x, b), s_mul(c.x, a));
+                acc.y = s_add(s_mul(acc.y, b), s_mul(c.y, a));
+                acc.z = s_add(s_mul(acc.z, b), s_mul(c.z, a));
+            }
+            acc.w = 1.0f;
+            __stcg(p.accum + idx, acc);
+            if (f + 1 == p.n_frames && p.primary_ids) p.primary_ids[idx] = primary;
+            if (p.cost) {
+                const unsigned dt = (unsigned)(clock64() - t_start);
+                p.cost[idx] = f == 0 ? dt : p.cost[idx] + dt;
+            }
+            __threadfence();
+        }
+        __syncwarp();
+        if (lane == 0) st_release_u32(progress + tile, f + 1);
+    }
+    for (int o = 16; o > 0; o >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o);
+    if (lane == 0 && nrays) atomicAdd(p.ray_counter, (unsigned long long)nrays);
+    flush_counts(cnt, p.work_counters);
+}
+
+template <class Cfg>
+cudaError_t launch_persistent(const RenderParams& p, int variant, int grid, cudaStream_t stream) {
+    const int tiles_x = (p.x1 - p.x0 + 7) >> 3;
+    const int bands = (p.y1 - p.y0 + 7) >> 3;
+    const int owned = bands > p.band_rank ? (bands - p.band_rank + p.band_world - 1) / p.band_world : 0;
+    if (owned == 0) return cudaSuccess;
+    const size_t ntiles = (size_t)tiles_x * owned * 2;
+    cudaError_t e = cudaMemsetAsync(p.sched, 0, (64 + ntiles) * sizeof(uint32_t), stream);
+    if (e != cudaSuccess) return e;
+    if (variant == 0) render_persistent<Cfg, 0><<<grid, 256, 0, stream>>>(p);
+    else if (variant == 1) render_persistent<Cfg, 1><<<grid, 256, 0, stream>>>(p);
+    else render_persistent<Cfg, 2><<<grid, 256, 0, stream>>>(p);
+    return cudaGetLastError();
 }
 
 template <class Cfg>

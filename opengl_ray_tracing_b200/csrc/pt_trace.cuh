@@ -126,19 +126,16 @@ struct WideState {
 // hitArray over one leaf.  `early`: this leaf is a FAR child being tested before the near subtree (its turn in
 // the reference's order comes later).  Exact-distance ties must still go to whoever the reference visits first:
 // an early hit needs strictly smaller t, and while an early hit is the best, in-turn candidates win ties.
-// TIE_DETECT (trace_fast, where the visiting order is not the reference's): an exact tie between two triangles is
-// not resolved here but reported, and the caller re-traces the ray on the reference topology.
-template <bool ANYHIT, bool TIE_DETECT>
+template <bool ANYHIT>
 __device__ __forceinline__ bool wide_leaf(const DevScene& sc, const Ray& r, uint32_t ref, bool early, int sp, WideState& st) {
     const uint32_t first = ref_index(ref), cnt = ref_count(ref);
     for (uint32_t i = first; i < first + cnt; i++) {
         const float4* g = sc.trigeo + 3 * (size_t)i;
         float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2);
         float tt; bool ins;
-        const bool allow_tie = TIE_DETECT ? (!ANYHIT && st.res.tri >= 0) : (!early && st.early_sp >= 0);
+        const bool allow_tie = !early && st.early_sp >= 0;
         if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), mk3(a.w, b.w, c.w), st.res.t, tt, ins,
                          allow_tie)) {
-            if (TIE_DETECT && !ANYHIT && tt == st.res.t) { st.tie = true; continue; }
             st.res.t = tt; st.res.tri = (int)i; st.res.inside = ins;
             if (ANYHIT) return true;
             st.cull = s_mul(tt, PT_CULL_SLACK);
@@ -159,7 +156,7 @@ __device__ __forceinline__ TraceResult trace_wide(const DevScene& sc, V3 origin,
     int sp = 0;
     uint32_t ref = sc.root_ref;
     if (ref_count(ref)) {                             // the whole scene is one leaf
-        wide_leaf<ANYHIT, false>(sc, r, ref, false, 0, st);
+        wide_leaf<ANYHIT>(sc, r, ref, false, 0, st);
         return st.res;
     }
     while (true) {
@@ -178,12 +175,12 @@ __device__ __forceinline__ TraceResult trace_wide(const DevScene& sc, V3 origin,
             const float ne = left_first ? e1 : e2, fe = left_first ? e2 : e1;
             const bool nleaf = ref_count(nref) != 0, fleaf = ref_count(fref) != 0;
             if (nleaf) {
-                if (ne <= st.cull && wide_leaf<ANYHIT, false>(sc, r, nref, false, sp, st)) return st.res;
-                if (fleaf) { if (fe <= st.cull && wide_leaf<ANYHIT, false>(sc, r, fref, false, sp, st)) return st.res; }
+                if (ne <= st.cull && wide_leaf<ANYHIT>(sc, r, nref, false, sp, st)) return st.res;
+                if (fleaf) { if (fe <= st.cull && wide_leaf<ANYHIT>(sc, r, fref, false, sp, st)) return st.res; }
                 else if (fe <= st.cull) next = fref;
             } else if (fleaf) {
                 // far leaf, near subtree: test the leaf NOW rather than defer it
-                if (fe <= st.cull && wide_leaf<ANYHIT, false>(sc, r, fref, true, sp, st)) return st.res;
+                if (fe <= st.cull && wide_leaf<ANYHIT>(sc, r, fref, true, sp, st)) return st.res;
                 if (ne <= st.cull) next = nref;
             } else {
                 const bool ng = ne <= st.cull, fg = fe <= st.cull;
@@ -198,7 +195,7 @@ __device__ __forceinline__ TraceResult trace_wide(const DevScene& sc, V3 origin,
             const uint32_t cref = h1 ? lref : rref;
             const float ce = h1 ? e1 : e2;
             if (ce <= st.cull) {
-                if (ref_count(cref)) { if (wide_leaf<ANYHIT, false>(sc, r, cref, false, sp, st)) return st.res; }
+                if (ref_count(cref)) { if (wide_leaf<ANYHIT>(sc, r, cref, false, sp, st)) return st.res; }
                 else next = cref;
             }
         }
@@ -216,59 +213,104 @@ __device__ __forceinline__ TraceResult trace_wide(const DevScene& sc, V3 origin,
 }
 
 // ---- the fast-topology traversal -------------------------------------------------------------------
-// Same node format, but over the binned-SAH tree of pt_build.cpp whose leaves are the reference's leaves.  A leaf
-// child's box in the parent IS the reference leaf's box, so `hit_aabb(...) > 0` on it is exactly the reference's
-// condition for visiting that leaf; inner boxes are unions of leaf boxes, hence conservative.  The visiting order
-// here is nearest-entry-first (not the reference's), which can only matter for an exact tie between two triangles:
-// that is detected (st.tie) and the ray is re-traced on the reference topology.
-template <bool ANYHIT, int STACK>
-__device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin, V3 dir) {
+// Same node format, over the binned-SAH tree pt_build.cpp builds over the individual triangles (boxes padded,
+// triangles re-ordered).  The padded boxes only CULL; what the reference's tree means for the result is applied
+// exactly, per candidate: a triangle that passes hitTriangle counts only if the ray also passes the reference's
+// hitAABB(...) > 0 on the box of the reference leaf that holds it (P:356-379; that implies all its ancestors).
+// The root is the one node the reference never box-tests (P:342-343).  The visiting order here is
+// nearest-entry-first (not the reference's), which can only matter for an exact tie between two triangles: that is
+// detected (st.tie) and the ray is re-traced on the reference topology.
+// Work counters of the fast traversal (DESIGN.md "Roofline"): compiled in only for the counting configuration.
+struct TraceCount {
+    uint32_t inner, tris, cand, ties;   // inner nodes fetched, triangles tested, candidates that reached the leaf-box test, tie re-traces
+};
+template <bool ON> struct Counter {
+    TraceCount c;
+    __device__ __forceinline__ Counter() { c.inner = c.tris = c.cand = c.ties = 0; }
+    __device__ __forceinline__ void inner() { c.inner++; }
+    __device__ __forceinline__ void tri() { c.tris++; }
+    __device__ __forceinline__ void cand() { c.cand++; }
+    __device__ __forceinline__ void tie() { c.ties++; }
+};
+template <> struct Counter<false> {
+    __device__ __forceinline__ void inner() {}
+    __device__ __forceinline__ void tri() {}
+    __device__ __forceinline__ void cand() {}
+    __device__ __forceinline__ void tie() {}
+};
+
+// While-while form (one node-test site, one triangle-test site: the hot loop is ~250 SASS instructions and stays
+// in the instruction cache): descend inner nodes — nearer child first, farther child pushed — until the current
+// ref is a leaf; test its triangles; pop.  Leaves travel through the stack like inner nodes.
+template <bool ANYHIT, int STACK, class CNT>
+__device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin, V3 dir, CNT& cnt) {
     Ray r = make_ray(origin, dir);
-    WideState st;
-    st.res.tri = -1; st.res.t = PT_INF; st.res.inside = false;
-    st.cull = PT_INF; st.early_sp = -1; st.tie = false;
+    TraceResult res; res.tri = -1; res.t = PT_INF; res.inside = false;
+    float cull = PT_INF;
+    bool tie = false;
     uint32_t stack_ref[STACK];
     float stack_t[STACK];
     int sp = 0;
     uint32_t ref = sc.root_fast;
-    if (ref_count(ref)) {
-        wide_leaf<ANYHIT, true>(sc, r, ref, false, 0, st);
-        return st.res;
-    }
     while (true) {
-        const float4* w = sc.wnodes_fast + 4 * (size_t)ref_index(ref);
-        float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
-        float e1, e2;
-        float d1 = hit_aabb(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), e1);
-        float d2 = hit_aabb(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), e2);
-        const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
-        bool g1 = (d1 > 0.0f) && (e1 <= st.cull), g2 = (d2 > 0.0f) && (e2 <= st.cull);
-        // leaf children are tested on the spot
-        if (g1 && ref_count(lref)) { if (wide_leaf<ANYHIT, true>(sc, r, lref, false, sp, st)) return st.res; g1 = false; }
-        if (g2 && ref_count(rref)) {
-            if (e2 <= st.cull && wide_leaf<ANYHIT, true>(sc, r, rref, false, sp, st)) return st.res;
-            g2 = false;
+        while (ref_count(ref) == 0) {                 // inner node: both child boxes and refs in one 64-byte record
+            const float4* w = sc.wnodes_fast + 4 * (size_t)ref;
+            const float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
+            cnt.inner();
+            float e1, e2;
+            const float d1 = hit_aabb(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), e1);
+            const float d2 = hit_aabb(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), e2);
+            const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+            const bool g1 = (d1 > 0.0f) && (e1 <= cull), g2 = (d2 > 0.0f) && (e2 <= cull);
+            if (g1 && g2) {
+                const bool left_first = e1 <= e2;
+                if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; return res; }
+                stack_ref[sp] = left_first ? rref : lref; stack_t[sp] = left_first ? e2 : e1; sp++;
+                ref = left_first ? lref : rref;
+            } else if (g1 || g2) {
+                ref = g1 ? lref : rref;
+            } else {
+                ref = PT_REF_NONE;
+                while (sp > 0) {
+                    sp--;
+                    if (stack_t[sp] <= cull) { ref = stack_ref[sp]; break; }
+                }
+                if (ref == PT_REF_NONE) goto done;
+            }
         }
-        g1 = g1 && (e1 <= st.cull);
-        g2 = g2 && (e2 <= st.cull);
-        if (g1 && g2) {
-            const bool left_first = e1 <= e2;
-            if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; break; }
-            stack_ref[sp] = left_first ? rref : lref; stack_t[sp] = left_first ? e2 : e1; sp++;
-            ref = left_first ? lref : rref;
-            continue;
+        {                                             // leaf: hitArray over its (re-ordered) triangles
+            const uint32_t first = ref_index(ref), end = first + ref_count(ref);
+            for (uint32_t i = first; i < end; i++) {
+                const float4* g = sc.trigeo_fast + 3 * (size_t)i;
+                const float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2);
+                cnt.tri();
+                float tt; bool ins;
+                if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), mk3(a.w, b.w, c.w), res.t, tt, ins,
+                                 !ANYHIT && res.tri >= 0)) {
+                    cnt.cand();
+                    const int2 meta = __ldg(sc.trimeta + i);
+                    if (meta.y != 1) {                // the reference never box-tests its root (P:342-343)
+                        const float* nd = sc.nodes_raw + 12 * (size_t)meta.y;
+                        float e;
+                        if (!(hit_aabb(r, raw3(nd + 6), raw3(nd + 9), e) > 0.0f)) continue;
+                    }
+                    if (!ANYHIT && tt == res.t) { tie = true; continue; }
+                    res.t = tt; res.tri = meta.x; res.inside = ins;
+                    if (ANYHIT) return res;
+                    cull = s_mul(tt, PT_CULL_SLACK);
+                }
+            }
         }
-        if (g1) { ref = lref; continue; }
-        if (g2) { ref = rref; continue; }
-        bool found = false;
+        ref = PT_REF_NONE;
         while (sp > 0) {
             sp--;
-            if (stack_t[sp] <= st.cull) { ref = stack_ref[sp]; found = true; break; }
+            if (stack_t[sp] <= cull) { ref = stack_ref[sp]; break; }
         }
-        if (!found) break;
+        if (ref == PT_REF_NONE) break;
     }
-    if (!ANYHIT && st.tie) st.res.tri = -2;           // caller: re-trace on the reference topology
-    return st.res;
+done:
+    if (!ANYHIT && tie) res.tri = -2;                 // caller: re-trace on the reference topology
+    return res;
 }
 
 // out-of-line so that the (practically never taken) tie path costs no registers in the hot loop

@@ -17,26 +17,28 @@ _LIB_PATH = os.path.join(_HERE, "libpt.so")
 _lib = None
 
 LAMBERT, DISNEY_UNIFORM, DISNEY_IS_MIS = 0, 1, 2
-MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE, MODE_PARITY_FAST = 0, 1, 2, 3
+MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE, MODE_PARITY_FAST, MODE_FAST_COUNT = 0, 1, 2, 3, 4
 DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 
 ACC_MEAN, ACC_SUM = 0, 1
+MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
-           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_last_error",
+           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_last_error",
            "pt_build_info"]
 
 
 class PtConfig(C.Structure):
     _fields_ = [("variant", C.c_int), ("width", C.c_int), ("height", C.c_int), ("max_bounce", C.c_int),
-                ("device", C.c_int), ("mode", C.c_int)]
+                ("device", C.c_int), ("mode", C.c_int), ("pipeline", C.c_int)]
 
 
 class PtStats(C.Structure):
     _fields_ = [("rays", C.c_ulonglong), ("samples", C.c_ulonglong), ("render_ms", C.c_double),
                 ("launches", C.c_ulonglong), ("max_stack_depth", C.c_int), ("n_inner_nodes", C.c_int),
                 ("n_materials", C.c_int), ("fast_tree_depth", C.c_int), ("n_fast_inner", C.c_int),
-                ("upload_build_ms", C.c_double)]
+                ("upload_build_ms", C.c_double), ("inner_visits", C.c_ulonglong), ("tri_tests", C.c_ulonglong),
+                ("leaf_candidates", C.c_ulonglong), ("tie_retraces", C.c_ulonglong)]
 
 
 class PtError(RuntimeError):
@@ -71,6 +73,7 @@ def lib():
         "pt_synchronize": (C.c_int, [vp]),
         "pt_get_stats": (C.c_int, [vp, C.POINTER(PtStats)]),
         "pt_reset_stats": (C.c_int, [vp]),
+        "pt_get_ray_histogram": (C.c_int, [vp, C.POINTER(C.c_ulonglong), C.c_int]),
         "pt_last_error": (C.c_char_p, []),
         "pt_build_info": (C.c_char_p, []),
     }
@@ -97,9 +100,10 @@ def _fp(a):
 class PathTracer:
     """pass1 of the reference (shader variant ``variant``) on CUDA device ``device``."""
 
-    def __init__(self, width, height, variant=DISNEY_IS_MIS, max_bounce=0, device=0, mode=MODE_FAST):
+    def __init__(self, width, height, variant=DISNEY_IS_MIS, max_bounce=0, device=0, mode=MODE_FAST, pipeline=MEGAKERNEL):
         self.width, self.height, self.variant, self.mode = width, height, variant, mode
-        cfg = PtConfig(variant, width, height, max_bounce, device, mode)
+        self.pipeline = pipeline
+        cfg = PtConfig(variant, width, height, max_bounce, device, mode, pipeline)
         h = C.c_void_p()
         _check(lib().pt_create(C.byref(cfg), C.byref(h)), "pt_create")
         self._h = h
@@ -187,6 +191,12 @@ class PathTracer:
         st = PtStats()
         _check(lib().pt_get_stats(self._h, C.byref(st)), "pt_get_stats")
         return {k: getattr(st, k) for k, _ in PtStats._fields_}
+
+    def ray_histogram(self):
+        """MODE_FAST_COUNT: bucket k = rays with 2^(k-1) <= traversal steps < 2^k."""
+        b = (C.c_ulonglong * 33)()
+        _check(lib().pt_get_ray_histogram(self._h, b, 33), "pt_get_ray_histogram")
+        return list(b)
 
     def reset_stats(self):
         _check(lib().pt_reset_stats(self._h), "pt_reset_stats")
