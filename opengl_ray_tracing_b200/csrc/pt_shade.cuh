@@ -57,17 +57,17 @@ __device__ __forceinline__ void note_ray(const Counter<true>& c, uint32_t before
     atomicAdd(hist + (n ? 32 - __clz(n) : 0), 1ull);
 }
 
-template <class Cfg, bool ANYHIT>
-__device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d, Counter<Cfg::COUNT>& cnt) {
-    if (Cfg::RAW) return trace_ref(sc, o, d);
+template <class Cfg>
+__device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d, const bool anyhit, Counter<Cfg::COUNT>& cnt) {
+    if (Cfg::RAW) return trace_ref(sc, o, d);         // the reference has no any-hit query: closest hit answers both
     if (Cfg::FAST_TREE) {
         const uint32_t steps0 = ray_steps(cnt);
-        TraceResult tr = trace_fast<ANYHIT, PT_STACK>(sc, o, d, cnt);
+        TraceResult tr = trace_fast<PT_STACK>(sc, o, d, anyhit, cnt);
         note_ray(cnt, steps0, sc.ray_histogram);
-        if (!ANYHIT && tr.tri == -2) { cnt.tie(); tr = trace_wide_fallback(sc, o, d); }   // exact tie: let the reference order decide
+        if (tr.tri == -2) { cnt.tie(); tr = trace_wide_fallback(sc, o, d); }   // exact tie: let the reference order decide
         return tr;
     }
-    return trace_wide<ANYHIT, PT_STACK>(sc, o, d);
+    return anyhit ? trace_wide<true, PT_STACK>(sc, o, d) : trace_wide<false, PT_STACK>(sc, o, d);
 }
 
 // ---- RNG and QMC -----------------------------------------------------------------------------------
@@ -147,6 +147,14 @@ template <class M> __device__ __forceinline__ void hdr_color_pdf(const DevScene&
     float sin_theta = fmaxf(M::sin(theta), 1e-10f);
     float p_convert = (float)(sc.hdrW * sc.hdrW / 2) / (2.0f * PT_PI * PT_PI * sin_theta);
     pdf_light = pdf * p_convert;
+}
+// hdrPdf at an already computed uv, P:655-666
+template <class M> __device__ __forceinline__ float hdr_pdf(const DevScene& sc, float u, float w) {
+    float pdf = tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, u, w).z;
+    float theta = PT_PI * (0.5f - w);
+    float sin_theta = fmaxf(M::sin(theta), 1e-10f);
+    float p_convert = (float)(sc.hdrW * sc.hdrW / 2) / (2.0f * PT_PI * PT_PI * sin_theta);
+    return pdf * p_convert;
 }
 template <class M> __device__ __forceinline__ V3 SampleHdr(const DevScene& sc, float xi_1, float xi_2) {   // P:573-585
     float4 c = tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, xi_1, xi_2);
@@ -325,6 +333,17 @@ __device__ __forceinline__ void generate_ray(const RenderParams& p, int px, int 
 
 // ---- one sample of one pixel: main() of the three shaders ------------------------------------------
 // Returns this frame's colour BEFORE accumulation; primary_id = triangle of the primary hit (-1 miss).
+// Written as a per-lane state machine around ONE traversal site: the ray in flight is the primary ray, a BRDF
+// bounce ray (closest hit) or an environment shadow ray (any hit); whatever must survive the traversal is a few
+// registers (f_r, N.L, pdf, history, Lo, and while a shadow ray flies: the pending bounce ray).  Lanes of a warp
+// whose paths are in different phases still run the traversal loop together, and the kernel holds one copy of the
+// traversal, one of the environment lookup and one of the BRDF evaluation (the megakernel's stall profile was
+// dominated by instruction fetch, profiles/r01_megakernel_v2.md).  Every value is computed by the same operations
+// in the same order as in the reference's straight-line code, so results are unchanged bit for bit.
+#define PT_PH_PRIMARY 0
+#define PT_PH_BOUNCE 1
+#define PT_PH_SHADOW 2
+
 template <class Cfg, int VARIANT>
 __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py, uint32_t frame, int& primary_id,
                                            uint32_t& nrays, Counter<Cfg::COUNT>& cnt) {
@@ -337,88 +356,107 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
 
     V3 Le0 = mk3(0, 0, 0), Lo = mk3(0, 0, 0), history = mk3(1, 1, 1);
     V3 f_r = mk3(0, 0, 0);
-    float cosw = 0.0f, pdf = 1.0f;                   // N·L (cosine_i) and the sampling pdf of the ray in flight
-    Material mat;
-    int bounce = -1;                                  // -1: the ray in flight is the primary ray
+    float cosw = 0.0f, pdf = 1.0f;                    // of the bounce ray in flight, or pending behind a shadow ray
+    V3 fl = mk3(0, 0, 0), nextL = mk3(0, 0, 0);       // shadow phase: BRDF value toward the light; the pending bounce ray
+    float ndl = 0.0f, pdf_b = 0.0f;                   //               N.Ld and the BRDF's pdf of Ld
+    bool next_ok = false;
+    int bounce = -1;
+    int phase = PT_PH_PRIMARY;
+    primary_id = -1;
     while (true) {
-        TraceResult tr = trace<Cfg, false>(sc, o, d, cnt);
+        const TraceResult tr = trace<Cfg>(sc, o, d, phase == PT_PH_SHADOW, cnt);
         nrays++;
-        Hit hit;
-        int mat_id;
-        finalize_hit<Cfg::RAW>(sc, o, d, tr, hit, mat_id);
-        if (bounce < 0) {
-            primary_id = tr.tri;
-            if (!hit.isHit) return sampleHdr<M>(sc, d);                                               // P:857-859
-            load_material<Cfg::RAW>(sc, mat_id, mat);
-            Le0 = mat.emissive;                                                                       // P:862
-        } else if (!hit.isHit) {
-            if (VARIANT == 2) {                                                                       // P:819-830
-                V3 color; float pdf_light;
-                hdr_color_pdf<M>(sc, d, color, pdf_light);
-                float mis_weight = misMixWeight(pdf, pdf_light);
-                Lo = Lo + (history * mis_weight) * color * f_r * cosw / pdf;
-            } else {                                                                                  // O:349-353, D:465-469
-                V3 sky = sampleHdr<M>(sc, d);
-                Lo = Lo + history * sky * f_r * cosw / pdf;
-            }
-            break;
-        } else {
-            load_material<Cfg::RAW>(sc, mat_id, mat);
-            Lo = Lo + history * mat.emissive * f_r * cosw / pdf;                                      // P:833-834
-            history = history * (f_r * cosw / pdf);                                                   // P:837
-        }
-        bounce++;
-        if (bounce >= p.max_bounce) break;
-
-        // ---- next bounce from `hit` with material `mat` ----
-        V3 V = -hit.viewDir, N = hit.normal;
-        V3 L;
-        if (VARIANT == 2) {
-            // light sampling through the hdrCache + shadow ray + MIS, P:770-793
-            float e1 = rnd(seed);
-            float e2 = rnd(seed);
-            V3 Ld = SampleHdr<M>(sc, e1, e2);
-            if (dot(N, Ld) > 0.0f) {
-                TraceResult sh = trace<Cfg, true>(sc, hit.hitPoint, Ld, cnt);
-                nrays++;
-                if (sh.tri < 0) {
-                    V3 color; float pdf_light;
-                    hdr_color_pdf<M>(sc, Ld, color, pdf_light);
-                    V3 fl = BRDF_Evaluate_iso<M>(V, N, Ld, mat);
-                    float pdf_b = BRDF_Pdf<M>(V, N, Ld, mat);
-                    float mis_weight = misMixWeight(pdf_light, pdf_b);
-                    Lo = Lo + (history * mis_weight) * color * fl * dot(N, Ld) / pdf_light;
+        if (tr.tri < 0) {
+            // ---- the ray left the scene: one environment lookup serves all three phases ----
+            float u, w;
+            spherical_uv(d, u, w);
+            const float4 c = tex_nearest(sc.hdr4, sc.hdrW, sc.hdrH, u, w);
+            if (phase == PT_PH_PRIMARY) return mk3(fminf(c.x, 10.0f), fminf(c.y, 10.0f), fminf(c.z, 10.0f));   // P:857-859
+            if (VARIANT == 2) {
+                const V3 color = mk3(c.x, c.y, c.z);                                                  // hdrColor, P:647-651
+                const float pdf_light = hdr_pdf<M>(sc, u, w);                                         // hdrPdf, P:655-666
+                if (phase == PT_PH_SHADOW) {                                                          // P:781-792
+                    const float mis_weight = misMixWeight(pdf_light, pdf_b);
+                    Lo = Lo + (history * mis_weight) * color * fl * ndl / pdf_light;
+                } else {                                                                              // P:819-830
+                    const float mis_weight = misMixWeight(pdf, pdf_light);
+                    Lo = Lo + (history * mis_weight) * color * f_r * cosw / pdf;
+                    break;
                 }
+            } else {                                                                                  // O:349-353, D:465-469
+                const V3 sky = mk3(fminf(c.x, 10.0f), fminf(c.y, 10.0f), fminf(c.z, 10.0f));
+                Lo = Lo + history * sky * f_r * cosw / pdf;
+                break;
             }
-            // BRDF sampling driven by Sobol + Cranley-Patterson, P:795-816
-            float u = sobol((uint32_t)bounce * 2u, (frame + 1u) ^ ((frame + 1u) >> 1));
-            float v = sobol((uint32_t)bounce * 2u + 1u, (frame + 1u) ^ ((frame + 1u) >> 1));
-            cranley_patterson(px, py, u, v);
-            float xi_3 = rnd(seed);
-            L = SampleBRDF<M>(u, v, xi_3, V, N, mat);
-            cosw = dot(N, L);
-            if (cosw <= 0.0f) break;
-            f_r = BRDF_Evaluate_iso<M>(V, N, L, mat);
-            pdf = BRDF_Pdf<M>(V, N, L, mat);
-            if (pdf <= 0.0f) break;                   // the reference traces this ray and then discards it (P:811-816)
-        } else {
-            // uniform hemisphere, O:334-346 / D:448-456
-            float z = rnd(seed);
-            float r = fmaxf(0.0f, sqrtf(1.0f - z * z));
-            float phi = 2.0f * PT_PI * rnd(seed);
-            L = toNormalHemisphere(mk3(r * M::cos(phi), r * M::sin(phi), z), N);
-            pdf = 1.0f / (2.0f * PT_PI);
-            cosw = fmaxf(0.0f, dot(L, N));
-            if (VARIANT == 1) {
-                V3 tangent, bitangent;
-                getTangent(N, tangent, bitangent);
-                f_r = BRDF_Evaluate_aniso<M>(V, N, L, tangent, bitangent, mat);
+        } else if (phase != PT_PH_SHADOW) {
+            // ---- closest hit of the primary or a bounce ray ----
+            Hit hit;
+            int mat_id;
+            finalize_hit<Cfg::RAW>(sc, o, d, tr, hit, mat_id);
+            Material mat;
+            load_material<Cfg::RAW>(sc, mat_id, mat);
+            if (phase == PT_PH_PRIMARY) {
+                primary_id = tr.tri;
+                Le0 = mat.emissive;                                                                   // P:862
             } else {
-                f_r = mat.baseColor / PT_PI;
+                Lo = Lo + history * mat.emissive * f_r * cosw / pdf;                                  // P:833-834
+                history = history * (f_r * cosw / pdf);                                               // P:837
             }
+            bounce++;
+            if (bounce >= p.max_bounce) break;
+            const V3 V = -hit.viewDir, N = hit.normal;
+            o = hit.hitPoint;
+            if (VARIANT == 2) {
+                // light sampling through the hdrCache, P:770-775: the shadow ray flies first, the BRDF ray waits
+                const float e1 = rnd(seed);
+                const float e2 = rnd(seed);
+                const V3 Ld = SampleHdr<M>(sc, e1, e2);
+                ndl = dot(N, Ld);
+                const bool want_shadow = ndl > 0.0f;
+                // BRDF sampling driven by Sobol + Cranley-Patterson, P:795-816
+                float su = sobol((uint32_t)bounce * 2u, (frame + 1u) ^ ((frame + 1u) >> 1));
+                float sv = sobol((uint32_t)bounce * 2u + 1u, (frame + 1u) ^ ((frame + 1u) >> 1));
+                cranley_patterson(px, py, su, sv);
+                const float xi_3 = rnd(seed);
+                const V3 L = SampleBRDF<M>(su, sv, xi_3, V, N, mat);
+                cosw = dot(N, L);
+                next_ok = cosw > 0.0f;
+                // BRDF value and pdf toward the light (k = 0) and along the sampled direction (k = 1): one code copy
+#pragma unroll 1
+                for (int k = 0; k < 2; k++) {
+                    if (k == 0 ? !want_shadow : !next_ok) continue;
+                    const V3 Lk = k == 0 ? Ld : L;
+                    const V3 f = BRDF_Evaluate_iso<M>(V, N, Lk, mat);
+                    const float pf = BRDF_Pdf<M>(V, N, Lk, mat);
+                    if (k == 0) { fl = f; pdf_b = pf; }
+                    else { f_r = f; pdf = pf; }
+                }
+                if (next_ok && pdf <= 0.0f) next_ok = false;  // the reference traces this ray and then discards it (P:811-816)
+                if (want_shadow) { phase = PT_PH_SHADOW; d = Ld; nextL = L; continue; }
+                if (!next_ok) break;
+                phase = PT_PH_BOUNCE; d = L;
+            } else {
+                // uniform hemisphere, O:334-346 / D:448-456
+                const float z = rnd(seed);
+                const float r = fmaxf(0.0f, sqrtf(1.0f - z * z));
+                const float phi = 2.0f * PT_PI * rnd(seed);
+                const V3 L = toNormalHemisphere(mk3(r * M::cos(phi), r * M::sin(phi), z), N);
+                pdf = 1.0f / (2.0f * PT_PI);
+                cosw = fmaxf(0.0f, dot(L, N));
+                if (VARIANT == 1) {
+                    V3 tangent, bitangent;
+                    getTangent(N, tangent, bitangent);
+                    f_r = BRDF_Evaluate_aniso<M>(V, N, L, tangent, bitangent, mat);
+                } else {
+                    f_r = mat.baseColor / PT_PI;
+                }
+                phase = PT_PH_BOUNCE; d = L;
+            }
+            continue;
         }
-        o = hit.hitPoint;
-        d = L;
+        // ---- a shadow ray has been resolved (occluded, or its light term added): release the pending bounce ray ----
+        if (!next_ok) break;
+        phase = PT_PH_BOUNCE; d = nextL;
     }
     return Le0 + Lo;
 }

@@ -239,11 +239,12 @@ template <> struct Counter<false> {
     __device__ __forceinline__ void tie() {}
 };
 
-// While-while form (one node-test site, one triangle-test site: the hot loop is ~250 SASS instructions and stays
+// `anyhit` is a run-time flag (shadow rays stop at the first accepted triangle): ONE copy of this loop serves every
+// ray of a path.  While-while form (one node-test site, one triangle-test site: the hot loop is ~250 SASS instructions and stays
 // in the instruction cache): descend inner nodes — nearer child first, farther child pushed — until the current
 // ref is a leaf; test its triangles; pop.  Leaves travel through the stack like inner nodes.
-template <bool ANYHIT, int STACK, class CNT>
-__device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin, V3 dir, CNT& cnt) {
+template <int STACK, class CNT>
+__device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin, V3 dir, const bool anyhit, CNT& cnt) {
     Ray r = make_ray(origin, dir);
     TraceResult res; res.tri = -1; res.t = PT_INF; res.inside = false;
     float cull = PT_INF;
@@ -286,7 +287,7 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
                 cnt.tri();
                 float tt; bool ins;
                 if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), mk3(a.w, b.w, c.w), res.t, tt, ins,
-                                 !ANYHIT && res.tri >= 0)) {
+                                 !anyhit && res.tri >= 0)) {
                     cnt.cand();
                     const int2 meta = __ldg(sc.trimeta + i);
                     if (meta.y != 1) {                // the reference never box-tests its root (P:342-343)
@@ -294,9 +295,9 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
                         float e;
                         if (!(hit_aabb(r, raw3(nd + 6), raw3(nd + 9), e) > 0.0f)) continue;
                     }
-                    if (!ANYHIT && tt == res.t) { tie = true; continue; }
+                    if (!anyhit && tt == res.t) { tie = true; continue; }
                     res.t = tt; res.tri = meta.x; res.inside = ins;
-                    if (ANYHIT) return res;
+                    if (anyhit) return res;
                     cull = s_mul(tt, PT_CULL_SLACK);
                 }
             }
@@ -309,7 +310,7 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
         if (ref == PT_REF_NONE) break;
     }
 done:
-    if (!ANYHIT && tie) res.tri = -2;                 // caller: re-trace on the reference topology
+    if (!anyhit && tie) res.tri = -2;                 // caller: re-trace on the reference topology
     return res;
 }
 

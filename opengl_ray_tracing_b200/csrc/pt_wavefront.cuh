@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) wf_generate(const __grid_constant__ Rende
                 uint32_t seed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + frame * 26699u) | 1u;     // P:73-76
                 V3 o, d;
                 generate_ray(p, px, py, seed, o, d);
-                const TraceResult tr = trace<Cfg, false>(p.sc, o, d, cnt);
+                const TraceResult tr = trace<Cfg>(p.sc, o, d, false, cnt);
                 nrays++;
                 if (write_ids) p.primary_ids[idx] = tr.tri;
                 if (tr.tri < 0) {
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(256) wf_shadow(const __grid_constant__ RenderP
             const uint32_t i = base + k + lane;
             if (i < count) {
                 const uint32_t idx = q[i];
-                const TraceResult sh = trace<Cfg, true>(p.sc, xyz(wf.ray_o[idx]), xyz(wf.sh_d[idx]), cnt);
+                const TraceResult sh = trace<Cfg>(p.sc, xyz(wf.ray_o[idx]), xyz(wf.sh_d[idx]), true, cnt);
                 nrays++;
                 if (sh.tri >= 0) wf.terms[(size_t)wf_light_slot(b) * wf.npaths + idx] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(256) wf_extend(const __grid_constant__ RenderP
                 idx = q[i];
                 const float4 ro = wf.ray_o[idx], rd = wf.ray_d[idx];
                 const V3 d = xyz(rd);
-                const TraceResult tr = trace<Cfg, false>(p.sc, xyz(ro), d, cnt);
+                const TraceResult tr = trace<Cfg>(p.sc, xyz(ro), d, false, cnt);
                 nrays++;
                 if (tr.tri < 0) {
                     const V3 history = xyz(wf.hist[idx]), f_r = xyz(wf.fr[idx]);

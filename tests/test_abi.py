@@ -36,7 +36,7 @@ def test_libptscene_exports_every_declared_symbol():
 def test_build_info_and_struct_layouts():
     info = R.build_info()
     assert "sm_100a" in info
-    assert C.sizeof(R.PtConfig) == 24 and C.sizeof(S.PtsMaterial) == 72
+    assert C.sizeof(R.PtConfig) == 28 and C.sizeof(R.PtStats) == 96 and C.sizeof(S.PtsMaterial) == 72
     # the cubin inside libpt.so really targets sm_100a
     import subprocess
     out = subprocess.run(["cuobjdump", "-lelf", os.path.join(ROOT, "opengl_ray_tracing_b200", "libpt.so")],
@@ -55,8 +55,9 @@ def test_no_cpu_fallback_without_a_device():
 def test_argument_validation_needs_no_gpu():
     L = R.lib()
     h = C.c_void_p()
-    for bad in (R.PtConfig(7, 16, 16, 0, 0, 0), R.PtConfig(0, 0, 16, 0, 0, 0), R.PtConfig(0, 16, 16, 0, 0, 9),
-                R.PtConfig(2, 16, 16, 5, 0, 0)):
+    for bad in (R.PtConfig(7, 16, 16, 0, 0, 0, 0), R.PtConfig(0, 0, 16, 0, 0, 0, 0), R.PtConfig(0, 16, 16, 0, 0, 9, 0),
+                R.PtConfig(2, 16, 16, 5, 0, 0, 0), R.PtConfig(0, 16, 16, 0, 0, 0, 7), R.PtConfig(0, 16, 16, 0, 0, 1, 1),
+                R.PtConfig(1, 16, 16, 9, 0, 0, 1)):
         assert L.pt_create(C.byref(bad), C.byref(h)) == -1          # PT_EINVAL before any CUDA call
         assert len(L.pt_last_error()) > 0
     assert L.pt_create(None, C.byref(h)) == -1
