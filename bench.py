@@ -11,7 +11,7 @@ A step = `--spp` frames (samples per pixel) of the whole 1080p image.  Prints ON
                    the fp32 framebuffer comes back to pinned host memory, inside the timed region
   roofline         the render kernel: algorithmic bytes (56 B per inner node visited, 36 B per
                    triangle tested, 108 B per shaded hit, 32 B per sample, 12 B per environment texel; the per-ray
-                   counts come from the oracle's culled traversal on a sample of this workload) / launch time
+                   counts come from the counting build of the same kernel on one frame of the whole image) / launch time
   cpu_baseline     the CPU oracle (OpenMP, all host cores) on a bounded crop of the same workload
 N > 1 (torchrun, one rank per GPU): the scene is replicated, the image is split in interleaved 8-row bands
 (one launch per rank), and every step ends with an NCCL reduce of the framebuffers to rank 0 — total work is
@@ -46,11 +46,12 @@ WORKLOADS = {
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="is-1M-1080p", choices=sorted(WORKLOADS))
-    ap.add_argument("--spp", type=int, default=8, help="frames (samples per pixel) per step")
+    ap.add_argument("--spp", type=int, default=64, help="frames (samples per pixel) per step")
+    ap.add_argument("--pipeline", type=int, default=2, help="0 megakernel, 1 wavefront, 2 persistent (production)")
     ap.add_argument("--split", default="tile", choices=["tile", "sample"])
     ap.add_argument("--mode", type=int, default=0, help="0 fast (production), 1 parity-ref, 2 parity-wide")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -60,7 +61,7 @@ def parse_args():
 
 # ---------------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks/throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks/throttle reasons sampled every 50 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -71,7 +72,7 @@ class ClockSampler(threading.Thread):
     def run(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
                 self.rows.append([c.strip() for c in line.split(",")])
@@ -201,7 +202,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sc, W, H, t_scene = build_workload(args.workload)
 
-    pt = R.PathTracer(W, H, sc.variant, device=local, mode=args.mode)
+    pt = R.PathTracer(W, H, sc.variant, device=local, mode=args.mode, pipeline=args.pipeline)
     t0 = time.perf_counter()
     pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache)
     t_upload = time.perf_counter() - t0
@@ -298,6 +299,7 @@ def run_ours(args):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "triangles": sc.nTriangles, "nodes": sc.nNodes, "variant": sc.variant,
                        "max_bounce": sc.max_bounce, "width": W, "height": H, "spp_per_step": spp, "mode": args.mode,
+                       "pipeline": {0: "megakernel", 1: "wavefront", 2: "persistent"}[args.pipeline],
                        "split": args.split if world > 1 else "none",
                        "l2": "flushed between steps (256 MiB fill)" if flush is not None else "not flushed",
                        "scene_bytes_hbm": int(sc.tris.nbytes + sc.nodes.nbytes + sc.nTriangles * 96 + st["n_inner_nodes"] * 64
@@ -309,27 +311,43 @@ def run_ours(args):
             "scene_build_s": t_scene, "scene_upload_s": t_upload, "wall_s_timed_region": t_wall,
             "kernel_ms_per_step": kern_ms / args.steps,
         }
-        # roofline of the render kernel + CPU baseline (oracle on a bounded crop, rank 0, N = 1 only)
-        if not args.no_cpu_baseline:
+        # roofline of the render kernel: algorithmic bytes from the kernel's OWN traversal counts (one frame of the
+        # whole image through the counting build of the same kernel, outside the timed region), SURVEY.md §8(d)
+        # coefficients: 56 B per inner node visited, 36 B per triangle tested, 108 B per shaded hit, 12 B per
+        # environment texel, 32 B per sample (accumulator read + write).
+        cpt = R.PathTracer(W, H, sc.variant, device=local, mode=R.MODE_FAST_COUNT, pipeline=R.PERSISTENT)
+        cpt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache)
+        cpt.set_camera(sc.eye, sc.cam)
+        if world > 1:
+            cpt.set_band_interleave(world, rank)
+        cpt.render_spp(0, 1)
+        cs = cpt.stats()
+        cpt.close()
+        bytes_per_ray = (56 * cs["inner_visits"] + 36 * cs["tri_tests"] + 108 * cs["shaded_hits"] + 12 * cs["env_texels"]
+                         + 32 * cs["samples"]) / max(1, cs["rays"])
+        achieved = (rays / world) * bytes_per_ray / (kern_ms * 1e-3) / 1e9          # per GPU, over kernel time
+        traffic = issue = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            with open(tpath) as f:
+                tj = json.load(f).get(args.workload, {})
+            traffic, issue = tj.get("dram_bytes_per_launch"), tj.get("issue")
+        line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                            "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
+                            "inner_per_ray": cs["inner_visits"] / max(1, cs["rays"]), "tris_per_ray": cs["tri_tests"] / max(1, cs["rays"]),
+                            "shaded_hits_per_ray": cs["shaded_hits"] / max(1, cs["rays"]), "texels_per_ray": cs["env_texels"] / max(1, cs["rays"]),
+                            "kernel": "render_persistent<CfgFast,%d>" % sc.variant, "kernel_ms_per_launch": kern_ms / max(1, launches / world),
+                            "issue": issue,
+                            "note": "the path is SM-issue/latency bound with an L2-resident working set (DESIGN.md); "
+                                    "traffic = ncu dram bytes of one launch of the committed capture (profiles/)"}
+        if not args.no_cpu_baseline and world == 1:
+            from oracle import pyoracle as O
             dt, _, npx, reg = cpu_sample(sc, W, H, math=1, frames=2, counters=False)
             _, cnt, _, _ = cpu_sample(sc, W, H, math=1, frames=1, counters=True)
-            from oracle import pyoracle as O
-            bytes_per_ray = (algorithmic_bytes(cnt) + 32 * npx) / cnt["rays"]
-            achieved = (rays / world) * bytes_per_ray / (kern_ms * 1e-3) / 1e9      # per GPU, over kernel time
-            traffic = None
-            tpath = os.path.join(ROOT, "profiles", "traffic.json")
-            if os.path.exists(tpath):
-                with open(tpath) as f:
-                    traffic = json.load(f).get(args.workload)
-            line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                                "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
-                                "inner_per_ray": cnt["cull_inner"] / cnt["rays"], "tris_per_ray": cnt["cull_tris"] / cnt["rays"],
-                                "note": "BVH traversal is latency/issue bound with an L2-resident working set; see profiles/"}
-            if world == 1:
-                cpu_rays = cnt["rays"] * 2          # 2 frames timed; per-frame ray counts differ by < 1 %
-                line["cpu_baseline"] = {"value": cpu_rays / dt / 1e6, "unit": "Mrays/s", "cores": O.num_threads(), "kind": "port",
-                                        "sample": "oracle (-O2 -fopenmp), centre crop %dx%d of %dx%d, 2 frames"
-                                                  % (reg[2] - reg[0], reg[3] - reg[1], W, H)}
+            cpu_rays = cnt["rays"] * 2          # 2 frames timed; per-frame ray counts differ by < 1 %
+            line["cpu_baseline"] = {"value": cpu_rays / dt / 1e6, "unit": "Mrays/s", "cores": O.num_threads(), "kind": "port",
+                                    "sample": "oracle (-O2 -fopenmp), centre crop %dx%d of %dx%d, 2 frames"
+                                              % (reg[2] - reg[0], reg[3] - reg[1], W, H)}
         print(json.dumps(line), flush=True)
     pt.close()
     if world > 1:

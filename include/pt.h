@@ -82,6 +82,8 @@ typedef struct PtStats {
     unsigned long long tri_tests;     /*   triangles tested */
     unsigned long long leaf_candidates; /* triangle hits that went through the reference-leaf box test */
     unsigned long long tie_retraces;  /*   rays re-traced on the reference topology because of an exact-distance tie */
+    unsigned long long shaded_hits;   /*   closest hits whose normals + material were fetched */
+    unsigned long long env_texels;    /*   environment-map and hdrCache texels fetched */
 } PtStats;
 
 typedef struct pt_ctx pt_ctx;

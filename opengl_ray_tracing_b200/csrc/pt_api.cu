@@ -537,8 +537,7 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
         e = fastmode ? pt::launch_wavefront_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
                      : pt::launch_wavefront_parity(p, c->cfg.variant, c->cfg.mode, grid, c->stream);
     } else if (persistent) {
-        // registers allow 2-3 CTAs of 256 threads per SM; surplus CTAs find the work list empty and leave
-        const int grid = (c->num_sms > 0 ? c->num_sms : 148) * 3;
+        const int grid = c->num_sms > 0 ? c->num_sms : 148;   // the launcher multiplies by the kernel's CTAs per SM
         e = fastmode ? pt::launch_persistent_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
                      : pt::launch_persistent_parity(p, c->cfg.variant, c->cfg.mode, grid, c->stream);
     } else {
@@ -654,9 +653,9 @@ int pt_get_stats(pt_ctx* c, PtStats* out) {
     CK(cudaStreamSynchronize(c->stream));
     int rc = collect_timing(c);
     if (rc != PT_OK) return rc;
-    unsigned long long cnt[5] = {0, 0, 0, 0, 0};
+    unsigned long long cnt[7] = {0, 0, 0, 0, 0, 0, 0};
     CK(cudaMemcpy(cnt, c->ray_counter, sizeof cnt, cudaMemcpyDeviceToHost));
-    out->rays = cnt[0]; out->inner_visits = cnt[1]; out->tri_tests = cnt[2]; out->leaf_candidates = cnt[3]; out->tie_retraces = cnt[4]; out->samples = c->samples; out->render_ms = c->render_ms; out->launches = c->launches;
+    out->rays = cnt[0]; out->inner_visits = cnt[1]; out->tri_tests = cnt[2]; out->leaf_candidates = cnt[3]; out->tie_retraces = cnt[4]; out->shaded_hits = cnt[5]; out->env_texels = cnt[6]; out->samples = c->samples; out->render_ms = c->render_ms; out->launches = c->launches;
     out->max_stack_depth = c->has_scene ? c->sc.stack_depth : 0;
     out->n_inner_nodes = c->has_scene ? c->sc.nInner : 0;
     out->n_materials = c->has_scene ? c->sc.nMaterials : 0;

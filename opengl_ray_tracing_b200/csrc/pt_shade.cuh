@@ -371,6 +371,7 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
             float u, w;
             spherical_uv(d, u, w);
             const float4 c = tex_nearest(sc.hdr4, sc.hdrW, sc.hdrH, u, w);
+            cnt.texel(VARIANT == 2 && phase != PT_PH_PRIMARY ? 2u : 1u);
             if (phase == PT_PH_PRIMARY) return mk3(fminf(c.x, 10.0f), fminf(c.y, 10.0f), fminf(c.z, 10.0f));   // P:857-859
             if (VARIANT == 2) {
                 const V3 color = mk3(c.x, c.y, c.z);                                                  // hdrColor, P:647-651
@@ -393,6 +394,7 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
             Hit hit;
             int mat_id;
             finalize_hit<Cfg::RAW>(sc, o, d, tr, hit, mat_id);
+            cnt.shaded();
             Material mat;
             load_material<Cfg::RAW>(sc, mat_id, mat);
             if (phase == PT_PH_PRIMARY) {
@@ -411,6 +413,7 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
                 const float e1 = rnd(seed);
                 const float e2 = rnd(seed);
                 const V3 Ld = SampleHdr<M>(sc, e1, e2);
+                cnt.texel(1u);
                 ndl = dot(N, Ld);
                 const bool want_shadow = ndl > 0.0f;
                 // BRDF sampling driven by Sobol + Cranley-Patterson, P:795-816
@@ -464,14 +467,16 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
 // adds a thread's traversal counters to the global ones (counting configuration only)
 __device__ __forceinline__ void flush_counts(Counter<false>&, unsigned long long*) {}
 __device__ __forceinline__ void flush_counts(Counter<true>& cnt, unsigned long long* out) {
-    uint32_t a = cnt.c.inner, b = cnt.c.tris, c = cnt.c.cand, d = cnt.c.ties;
+    uint32_t a = cnt.c.inner, b = cnt.c.tris, c = cnt.c.cand, d = cnt.c.ties, e = cnt.c.shaded, f = cnt.c.texels;
     for (int o = 16; o > 0; o >>= 1) {
         a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); c += __shfl_xor_sync(0xffffffffu, c, o);
         d += __shfl_xor_sync(0xffffffffu, d, o);
+        e += __shfl_xor_sync(0xffffffffu, e, o); f += __shfl_xor_sync(0xffffffffu, f, o);
     }
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(out, (unsigned long long)a); atomicAdd(out + 1, (unsigned long long)b); atomicAdd(out + 2, (unsigned long long)c);
         if (d) atomicAdd(out + 3, (unsigned long long)d);
+        atomicAdd(out + 4, (unsigned long long)e); atomicAdd(out + 5, (unsigned long long)f);
     }
 }
 
@@ -533,8 +538,11 @@ __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+#ifndef PT_PERSIST_MIN_CTAS
+#define PT_PERSIST_MIN_CTAS 6           // measured on B200 (is-1M / lambert-100k / disney-1M, Grays/s): 3 CTAs 11.6/5.7/5.3, 4: 12.4/6.5/6.1, 6: 12.6/7.0/6.8, 8: 12.1/6.9/6.7
+#endif
 template <class Cfg, int VARIANT>
-__global__ void __launch_bounds__(256) render_persistent(const __grid_constant__ RenderParams p) {
+__global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(const __grid_constant__ RenderParams p) {
     const int lane = threadIdx.x & 31;
     const int tiles_x = (p.x1 - p.x0 + 7) >> 3;
     const int bands = (p.y1 - p.y0 + 7) >> 3;
@@ -593,7 +601,7 @@ __global__ void __launch_bounds__(256) render_persistent(const __grid_constant__
 }
 
 template <class Cfg>
-cudaError_t launch_persistent(const RenderParams& p, int variant, int grid, cudaStream_t stream) {
+cudaError_t launch_persistent(const RenderParams& p, int variant, int num_sms, cudaStream_t stream) {
     const int tiles_x = (p.x1 - p.x0 + 7) >> 3;
     const int bands = (p.y1 - p.y0 + 7) >> 3;
     const int owned = bands > p.band_rank ? (bands - p.band_rank + p.band_world - 1) / p.band_world : 0;
@@ -601,9 +609,15 @@ cudaError_t launch_persistent(const RenderParams& p, int variant, int grid, cuda
     const size_t ntiles = (size_t)tiles_x * owned * 2;
     cudaError_t e = cudaMemsetAsync(p.sched, 0, (64 + ntiles) * sizeof(uint32_t), stream);
     if (e != cudaSuccess) return e;
-    if (variant == 0) render_persistent<Cfg, 0><<<grid, 256, 0, stream>>>(p);
-    else if (variant == 1) render_persistent<Cfg, 1><<<grid, 256, 0, stream>>>(p);
-    else render_persistent<Cfg, 2><<<grid, 256, 0, stream>>>(p);
+    // one resident set of CTAs: SMs x (CTAs that fit per SM), never more warps than there are tiles
+    void (*kern)(const RenderParams) = variant == 0 ? render_persistent<Cfg, 0> : variant == 1 ? render_persistent<Cfg, 1> : render_persistent<Cfg, 2>;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0);
+    if (e != cudaSuccess) return e;
+    int grid = num_sms * (per_sm > 0 ? per_sm : 1);
+    const int need = (int)((ntiles + 7) / 8);
+    if (grid > need) grid = need;
+    kern<<<grid, 256, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

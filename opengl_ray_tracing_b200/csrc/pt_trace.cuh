@@ -222,21 +222,25 @@ __device__ __forceinline__ TraceResult trace_wide(const DevScene& sc, V3 origin,
 // detected (st.tie) and the ray is re-traced on the reference topology.
 // Work counters of the fast traversal (DESIGN.md "Roofline"): compiled in only for the counting configuration.
 struct TraceCount {
-    uint32_t inner, tris, cand, ties;   // inner nodes fetched, triangles tested, candidates that reached the leaf-box test, tie re-traces
+    uint32_t inner, tris, cand, ties, shaded, texels;   // inner nodes fetched, triangles tested, candidates that reached the leaf-box test, tie re-traces
 };
 template <bool ON> struct Counter {
     TraceCount c;
-    __device__ __forceinline__ Counter() { c.inner = c.tris = c.cand = c.ties = 0; }
+    __device__ __forceinline__ Counter() { c.inner = c.tris = c.cand = c.ties = c.shaded = c.texels = 0; }
     __device__ __forceinline__ void inner() { c.inner++; }
     __device__ __forceinline__ void tri() { c.tris++; }
     __device__ __forceinline__ void cand() { c.cand++; }
     __device__ __forceinline__ void tie() { c.ties++; }
+    __device__ __forceinline__ void shaded() { c.shaded++; }     // closest hits whose shading data is fetched
+    __device__ __forceinline__ void texel(uint32_t n) { c.texels += n; }   // environment map / hdrCache texels fetched
 };
 template <> struct Counter<false> {
     __device__ __forceinline__ void inner() {}
     __device__ __forceinline__ void tri() {}
     __device__ __forceinline__ void cand() {}
     __device__ __forceinline__ void tie() {}
+    __device__ __forceinline__ void shaded() {}
+    __device__ __forceinline__ void texel(uint32_t) {}
 };
 
 // `anyhit` is a run-time flag (shadow rays stop at the first accepted triangle): ONE copy of this loop serves every

@@ -38,7 +38,8 @@ class PtStats(C.Structure):
                 ("launches", C.c_ulonglong), ("max_stack_depth", C.c_int), ("n_inner_nodes", C.c_int),
                 ("n_materials", C.c_int), ("fast_tree_depth", C.c_int), ("n_fast_inner", C.c_int),
                 ("upload_build_ms", C.c_double), ("inner_visits", C.c_ulonglong), ("tri_tests", C.c_ulonglong),
-                ("leaf_candidates", C.c_ulonglong), ("tie_retraces", C.c_ulonglong)]
+                ("leaf_candidates", C.c_ulonglong), ("tie_retraces", C.c_ulonglong), ("shaded_hits", C.c_ulonglong),
+                ("env_texels", C.c_ulonglong)]
 
 
 class PtError(RuntimeError):
@@ -100,7 +101,7 @@ def _fp(a):
 class PathTracer:
     """pass1 of the reference (shader variant ``variant``) on CUDA device ``device``."""
 
-    def __init__(self, width, height, variant=DISNEY_IS_MIS, max_bounce=0, device=0, mode=MODE_FAST, pipeline=MEGAKERNEL):
+    def __init__(self, width, height, variant=DISNEY_IS_MIS, max_bounce=0, device=0, mode=MODE_FAST, pipeline=PERSISTENT):
         self.width, self.height, self.variant, self.mode = width, height, variant, mode
         self.pipeline = pipeline
         cfg = PtConfig(variant, width, height, max_bounce, device, mode, pipeline)

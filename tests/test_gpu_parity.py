@@ -23,9 +23,10 @@ def R():
     return renderer
 
 
-def render(R, sc, W, H, first, n, mode, region=None, max_bounce=0, pt=None, close=True):
+def render(R, sc, W, H, first, n, mode, region=None, max_bounce=0, pt=None, close=True, pipeline=None):
     if pt is None:
-        pt = R.PathTracer(W, H, sc.variant, max_bounce=max_bounce, mode=mode)
+        pt = R.PathTracer(W, H, sc.variant, max_bounce=max_bounce, mode=mode,
+                          pipeline=R.PERSISTENT if pipeline is None else pipeline)
         pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache)
         pt.set_camera(sc.eye, sc.cam)
     if region:
@@ -194,3 +195,102 @@ def test_error_behaviour(R):
     with pytest.raises(R.PtError, match="max_bounce"):
         R.PathTracer(8, 8, 2, max_bounce=5)
     pt.close()
+
+
+# ---- the three schedulings of the same arithmetic: megakernel, wavefront, persistent -------------------------------
+PIPELINES = [0, 1, 2]
+
+
+@pytest.mark.parametrize("kind", sorted(KINDS))
+@pytest.mark.parametrize("pipeline", PIPELINES)
+def test_every_pipeline_is_bit_identical_to_the_oracle(R, kind, pipeline):
+    sc = small_scene(kind, "10k", hdr_res=(512, 256), camera=(10.0, 25.0, 2.5))
+    W, H, NF = 210, 77, 3                                    # ragged against 8x4 warp tiles and 32x8 CTA tiles
+    ref, ids_ref, _ = oracle_render(sc, W, H, 0, NF)
+    for mode in (R.MODE_PARITY_WIDE, R.MODE_PARITY_FAST):
+        img, ids, st, _ = render(R, sc, W, H, 0, NF, mode, pipeline=pipeline)
+        assert img.tobytes() == ref.tobytes(), "pipeline %d mode %d not bit-identical to the oracle" % (pipeline, mode)
+        assert (ids == ids_ref).all()
+    img, ids, st, _ = render(R, sc, W, H, 0, NF, R.MODE_FAST, pipeline=pipeline)
+    assert (ids == ids_ref).all() and rrmse(img, ref) <= RRMSE_TOL
+    assert st["rays"] > W * H * NF and st["launches"] >= 1
+
+
+@pytest.mark.parametrize("pipeline", PIPELINES)
+def test_pipelines_continue_frames_split_regions_and_sum(R, pipeline):
+    sc = small_scene("is", "1k")
+    W, H, NF = 100, 52, 4
+    full, _, _, _ = render(R, sc, W, H, 0, NF, R.MODE_PARITY_FAST, pipeline=0)
+    # frame continuation in two calls
+    img, _, _, pt = render(R, sc, W, H, 0, 1, R.MODE_PARITY_FAST, pipeline=pipeline, close=False)
+    img, _, _, _ = render(R, sc, W, H, 1, NF - 1, R.MODE_PARITY_FAST, pt=pt)
+    assert img.tobytes() == full.tobytes()
+    # three rectangles tile the image
+    pt = R.PathTracer(W, H, sc.variant, mode=R.MODE_PARITY_FAST, pipeline=pipeline)
+    pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); pt.set_camera(sc.eye, sc.cam)
+    for reg in [(0, 0, 37, H), (37, 0, W, 19), (37, 19, W, H)]:
+        pt.set_region(*reg); pt.render_spp(0, NF)
+    assert pt.readback().tobytes() == full.tobytes()
+    pt.close()
+    # interleaved bands over 3 ranks
+    parts = []
+    for rank in range(3):
+        q = R.PathTracer(W, H, sc.variant, mode=R.MODE_PARITY_FAST, pipeline=pipeline)
+        q.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); q.set_camera(sc.eye, sc.cam)
+        q.set_band_interleave(3, rank); q.render_spp(0, NF)
+        parts.append(q.readback()); q.close()
+    assert (parts[0] + parts[1] + parts[2]).tobytes() == full.tobytes()
+    # sample split: strided frames as plain sums
+    acc = np.zeros_like(full)
+    for rank in range(2):
+        q = R.PathTracer(W, H, sc.variant, mode=R.MODE_PARITY_FAST, pipeline=pipeline)
+        q.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); q.set_camera(sc.eye, sc.cam)
+        q.render_frames(rank, NF // 2, 2, R.ACC_SUM)
+        acc += q.readback(); q.close()
+    acc[..., :3] /= NF
+    assert rrmse(acc, full) < 1e-5
+
+
+def test_metric_scene_every_pipeline(R):
+    """is-1M (the metric scene) at a quarter of 1080p: all pipelines give the oracle's bits under the parity arithmetic."""
+    sc = small_scene("is", "1M", hdr_res=(1024, 512), camera=(0.0, 0.0, 4.0))
+    W, H = 480, 270
+    ref, ids_ref, _ = oracle_render(sc, W, H, 0, 2)
+    for pipeline in PIPELINES:
+        img, ids, _, _ = render(R, sc, W, H, 0, 2, R.MODE_PARITY_FAST, pipeline=pipeline)
+        assert img.tobytes() == ref.tobytes() and (ids == ids_ref).all(), "pipeline %d" % pipeline
+    # a close-up (camera inside the reference tree's degenerate region: the mesh fills the image)
+    from opengl_ray_tracing_b200 import scene as S
+    eye, cam = S.camera(20.0, 35.0, 1.2)
+    ref, ids_ref, _ = oracle_render(type(sc)(sc.name, sc.variant, sc.max_bounce, sc.tris, sc.nodes, sc.hdr, sc.hdrCache, eye, cam), 160, 90, 0, 1)
+    pt = R.PathTracer(160, 90, sc.variant, mode=R.MODE_PARITY_FAST)
+    pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); pt.set_camera(eye, cam); pt.render_spp(0, 1)
+    assert pt.readback().tobytes() == ref.tobytes() and (pt.readback_primary_ids() == ids_ref).all()
+    assert (ids_ref >= 0).mean() > 0.5
+    pt.close()
+
+
+def test_counting_build_and_cost_map(R):
+    sc = small_scene("is", "10k", hdr_res=(256, 128))
+    W, H, NF = 128, 72, 2
+    a, _, sa, _ = render(R, sc, W, H, 0, NF, R.MODE_FAST)
+    pt = R.PathTracer(W, H, sc.variant, mode=R.MODE_FAST_COUNT)
+    pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); pt.set_camera(sc.eye, sc.cam)
+    pt.enable_cost_map(True)
+    pt.render_spp(0, NF)
+    b, st = pt.readback(), pt.stats()
+    assert a.tobytes() == b.tobytes(), "the counting build must not change the image"
+    assert st["rays"] == sa["rays"] and st["inner_visits"] > 0 and st["tri_tests"] > 0
+    assert 0 < st["shaded_hits"] <= st["rays"] and st["env_texels"] > 0 and st["leaf_candidates"] <= st["tri_tests"]
+    assert sum(pt.ray_histogram()) == st["rays"]
+    cost = pt.readback_cost_map()
+    assert cost.shape == (H, W) and (cost > 0).all()
+    pt.close()
+    assert sa["inner_visits"] == 0                           # the production build carries no counters
+
+
+def test_wavefront_rejects_what_it_cannot_run(R):
+    with pytest.raises(R.PtError, match="megakernel only"):
+        R.PathTracer(8, 8, 0, mode=R.MODE_PARITY_REF, pipeline=R.WAVEFRONT)
+    with pytest.raises(R.PtError, match="max_bounce"):
+        R.PathTracer(8, 8, 1, max_bounce=9, pipeline=R.WAVEFRONT)
