@@ -538,6 +538,7 @@ __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+#define PT_PERSIST_CHUNK 1              // (tile, frame) items claimed per atomic
 #ifndef PT_PERSIST_MIN_CTAS
 #define PT_PERSIST_MIN_CTAS 6           // measured on B200 (is-1M / lambert-100k / disney-1M, Grays/s): 3 CTAs 11.6/5.7/5.3, 4: 12.4/6.5/6.1, 6: 12.6/7.0/6.8, 8: 12.1/6.9/6.7
 #endif
@@ -554,46 +555,51 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
     uint32_t nrays = 0;
     Counter<Cfg::COUNT> cnt;
     for (;;) {
-        uint32_t item = 0;
-        if (lane == 0) item = atomicAdd(head, 1u);
-        item = __shfl_sync(0xffffffffu, item, 0);
-        if (item >= nitems) break;
-        const uint32_t f = item / ntiles, tile = item - f * ntiles;
-        const uint32_t strip = tile / (uint32_t)tiles_x, tx = tile - strip * (uint32_t)tiles_x;
-        const int px = p.x0 + (int)tx * 8 + (lane & 7);
-        const int py = p.y0 + ((int)(strip >> 1) * p.band_world + p.band_rank) * 8 + (int)(strip & 1u) * 4 + (lane >> 3);
-        const bool valid = px < p.x1 && py < p.y1;
-        const uint32_t frame = p.first_frame + f * p.frame_stride;
-        const long long t_start = p.cost ? clock64() : 0;
-        V3 c = mk3(0, 0, 0);
-        int primary = -1;
-        if (valid) c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays, cnt);
-        // ordered accumulation
-        if (lane == 0) while (ld_acquire_u32(progress + tile) != f) __nanosleep(32);
-        __syncwarp();
-        if (valid) {
-            const size_t idx = (size_t)py * p.width + px;
-            float4 acc = __ldcg(p.accum + idx);        // L2: another SM wrote the previous frame
-            if (p.accumulate_sum) {
-                acc.x = s_add(acc.x, c.x); acc.y = s_add(acc.y, c.y); acc.z = s_add(acc.z, c.z);
-            } else {
-                float a = s_div(1.0f, (float)(frame + 1u));
-                float b = s_sub(1.0f, a);
-                acc.x = s_add(s_mul(acc.x, b), s_mul(c.x, a));
-                acc.y = s_add(s_mul(acc.y, b), s_mul(c.y, a));
-                acc.z = s_add(s_mul(acc.z, b), s_mul(c.z, a));
+        uint32_t first_item = 0;
+        if (lane == 0) first_item = atomicAdd(head, (uint32_t)PT_PERSIST_CHUNK);
+        first_item = __shfl_sync(0xffffffffu, first_item, 0);
+        if (first_item >= nitems) break;
+        // a claimed chunk is worked off in increasing item order; the item a warp may have to wait for (same tile, previous
+        // frame = item - ntiles) always lies in an EARLIER chunk, so waits point strictly backwards: no deadlock
+#pragma unroll 1
+        for (uint32_t item = first_item; item < first_item + PT_PERSIST_CHUNK && item < nitems; item++) {
+            const uint32_t f = item / ntiles, tile = item - f * ntiles;
+            const uint32_t strip = tile / (uint32_t)tiles_x, tx = tile - strip * (uint32_t)tiles_x;
+            const int px = p.x0 + (int)tx * 8 + (lane & 7);
+            const int py = p.y0 + ((int)(strip >> 1) * p.band_world + p.band_rank) * 8 + (int)(strip & 1u) * 4 + (lane >> 3);
+            const bool valid = px < p.x1 && py < p.y1;
+            const uint32_t frame = p.first_frame + f * p.frame_stride;
+            const long long t_start = p.cost ? clock64() : 0;
+            V3 c = mk3(0, 0, 0);
+            int primary = -1;
+            if (valid) c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays, cnt);
+            // ordered accumulation
+            if (lane == 0) while (ld_acquire_u32(progress + tile) != f) __nanosleep(32);
+            __syncwarp();
+            if (valid) {
+                const size_t idx = (size_t)py * p.width + px;
+                float4 acc = __ldcg(p.accum + idx);        // L2: another SM wrote the previous frame
+                if (p.accumulate_sum) {
+                    acc.x = s_add(acc.x, c.x); acc.y = s_add(acc.y, c.y); acc.z = s_add(acc.z, c.z);
+                } else {
+                    float a = s_div(1.0f, (float)(frame + 1u));
+                    float b = s_sub(1.0f, a);
+                    acc.x = s_add(s_mul(acc.x, b), s_mul(c.x, a));
+                    acc.y = s_add(s_mul(acc.y, b), s_mul(c.y, a));
+                    acc.z = s_add(s_mul(acc.z, b), s_mul(c.z, a));
+                }
+                acc.w = 1.0f;
+                __stcg(p.accum + idx, acc);
+                if (f + 1 == p.n_frames && p.primary_ids) p.primary_ids[idx] = primary;
+                if (p.cost) {
+                    const unsigned dt = (unsigned)(clock64() - t_start);
+                    p.cost[idx] = f == 0 ? dt : p.cost[idx] + dt;
+                }
             }
-            acc.w = 1.0f;
-            __stcg(p.accum + idx, acc);
-            if (f + 1 == p.n_frames && p.primary_ids) p.primary_ids[idx] = primary;
-            if (p.cost) {
-                const unsigned dt = (unsigned)(clock64() - t_start);
-                p.cost[idx] = f == 0 ? dt : p.cost[idx] + dt;
-            }
-            __threadfence();
+            // publish: the warp barrier orders every lane's store before lane 0's fence, whose release is cumulative
+            __syncwarp();
+            if (lane == 0) { __threadfence(); st_release_u32(progress + tile, f + 1); }
         }
-        __syncwarp();
-        if (lane == 0) st_release_u32(progress + tile, f + 1);
     }
     for (int o = 16; o > 0; o >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o);
     if (lane == 0 && nrays) atomicAdd(p.ray_counter, (unsigned long long)nrays);

@@ -49,7 +49,13 @@ __device__ __forceinline__ bool hit_triangle(const Ray& r, V3 p1, V3 p2, V3 p3, 
                                              bool& inside, bool allow_tie = false) {
     float Nd = s_dot(N, r.d);
     if (fabsf(Nd) < 0.00001f) return false;
-    float t = s_div(s_sub(s_dot(N, p1), s_dot(r.o, N)), Nd);
+    const float num = s_sub(s_dot(N, p1), s_dot(r.o, N));
+    // t = num / Nd can only reach 0.0005 if num and Nd have the same sign and num is not 0 (|Nd| >= 1e-5, so a product that
+    // underflows to 0 means t < 1e-35): everything else is rejected WITHOUT the division — same decision, and it keeps the
+    // exact-zero numerators of rays that start on the plane of the triangle (every secondary ray leaving a flat floor) off
+    // the IEEE divide's slow path (8 M warp-level slow-path calls per 64-frame launch on is-1M, profiles/r01_render_persistent.md).
+    if (!(s_mul(num, Nd) > 0.0f) && !(num != num)) return false;
+    float t = s_div(num, Nd);
     if (t < 0.0005f) return false;
     if (!(t < best) && !(allow_tie && t == best)) return false;
     V3 P = s_point(r.o, r.d, t);
@@ -323,6 +329,13 @@ static __device__ __noinline__ TraceResult trace_wide_fallback(const DevScene& s
     return trace_wide<false, PT_STACK>(sc, origin, dir);
 }
 
+// a / b with the IEEE result, taking the common exact-zero numerator (horizontal triangles: the xy-only barycentrics
+// of P:293-295 degenerate) around the divide's slow path: 0 / b = 0 * b (same signed zero) for every b except 0 and NaN/inf
+__device__ __forceinline__ float div_z(float a, float b) {
+    if (a == 0.0f && b != 0.0f && fabsf(b) <= 3.0e38f) return s_mul(a, b);
+    return s_div(a, b);
+}
+
 // ---- what the shader's HitResult carries for the winning triangle (P:285-299) -------------------
 template <bool RAW_LAYOUT>
 __device__ __forceinline__ void finalize_hit(const DevScene& sc, V3 origin, V3 dir, const TraceResult& tr, Hit& h,
@@ -350,10 +363,10 @@ __device__ __forceinline__ void finalize_hit(const DevScene& sc, V3 origin, V3 d
     V3 P = s_point(origin, dir, tr.t);
     h.hitPoint = P;
     // P:293-297 — barycentrics from x and y only, with the author's 5e-5 offsets
-    float alpha = (-(P.x - p2.x) * (p3.y - p2.y) + (P.y - p2.y) * (p3.x - p2.x)) /
-                  (-(p1.x - p2.x - 0.00005f) * (p3.y - p2.y + 0.00005f) + (p1.y - p2.y + 0.00005f) * (p3.x - p2.x + 0.00005f));
-    float beta = (-(P.x - p3.x) * (p1.y - p3.y) + (P.y - p3.y) * (p1.x - p3.x)) /
-                 (-(p2.x - p3.x - 0.00005f) * (p1.y - p3.y + 0.00005f) + (p2.y - p3.y + 0.00005f) * (p1.x - p3.x + 0.00005f));
+    float alpha = div_z(-(P.x - p2.x) * (p3.y - p2.y) + (P.y - p2.y) * (p3.x - p2.x),
+                        -(p1.x - p2.x - 0.00005f) * (p3.y - p2.y + 0.00005f) + (p1.y - p2.y + 0.00005f) * (p3.x - p2.x + 0.00005f));
+    float beta = div_z(-(P.x - p3.x) * (p1.y - p3.y) + (P.y - p3.y) * (p1.x - p3.x),
+                       -(p2.x - p3.x - 0.00005f) * (p1.y - p3.y + 0.00005f) + (p2.y - p3.y + 0.00005f) * (p1.x - p3.x + 0.00005f));
     float gama = 1.0f - alpha - beta;
     V3 Ns = normalize(n1 * alpha + n2 * beta + n3 * gama);
     h.normal = tr.inside ? -Ns : Ns;

@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <deque>
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -70,15 +71,9 @@ struct Builder {
     Rec* recs;
     int leaf_n;
     bool sah;
-    int task_cutoff;                                  // ranges larger than this spawn tasks (0 = never)
 
-    // Appends the subtree over recs[l..r] to `out` with ids relative to out's own start + base, where
-    // `base` is the absolute id the subtree root will have.  Returns the root's absolute id.
-    int build(std::vector<Node>& out, int base, int l, int r) {
-        if (l > r) return 0;
-        const size_t me = out.size();
-        out.push_back(Node());
-        Node nd;
+    // bounds of recs[l..r] into nd (M:381-393 / M:436-448)
+    void init_node(Node& nd, int l, int r) const {
         nd.left = nd.right = nd.n = nd.index = 0;
         nd.AA = V3{kInf, kInf, kInf};
         nd.BB = V3{-kInf, -kInf, -kInf};
@@ -87,43 +82,66 @@ struct Builder {
             nd.AA.x = mn(nd.AA.x, t.mnx); nd.AA.y = mn(nd.AA.y, t.mny); nd.AA.z = mn(nd.AA.z, t.mnz);
             nd.BB.x = mx(nd.BB.x, t.mxx); nd.BB.y = mx(nd.BB.y, t.mxy); nd.BB.z = mx(nd.BB.z, t.mxz);
         }
-        const int count = r - l + 1;
-        if (count <= leaf_n) {
-            nd.n = count;
-            nd.index = l;
-            out[me] = nd;
-            return base;
+    }
+
+    // sorts recs[l..r] the way the reference does at this node and returns the split position
+    int split_node(const Node& nd, int l, int r) {
+        if (sah) return sah_split(l, r);
+        float lenx = nd.BB.x - nd.AA.x, leny = nd.BB.y - nd.AA.y, lenz = nd.BB.z - nd.AA.z;
+        // three independent ifs, not else-ifs (M:412-420): ties sort more than once
+        if (lenx >= leny && lenx >= lenz) sort_axis(recs + l, recs + r + 1, 0);
+        if (leny >= lenx && leny >= lenz) sort_axis(recs + l, recs + r + 1, 1);
+        if (lenz >= lenx && lenz >= leny) sort_axis(recs + l, recs + r + 1, 2);
+        return (l + r) / 2;
+    }
+
+    // The reference recurses (left subtree, then right subtree, node ids handed out in preorder by push_back).  Its own
+    // SAH trees are thousands of levels deep on large meshes (6781 at 1 M triangles), so nothing here recurses: this
+    // builds the subtree over recs[l..r] into `out` with an explicit stack.  Child ids are relative to the subtree
+    // root's id `base` (id of a node = base + its position in `out` - position of the root).
+    void build_seq(std::vector<Node>& out, int base, int l, int r) {
+        if (l > r) return;
+        struct Frame { size_t me; int l, r, split, state; };
+        std::vector<Frame> st;
+        const size_t root = out.size();
+        out.push_back(Node());
+        st.push_back(Frame{root, l, r, 0, 0});
+        while (!st.empty()) {
+            Frame& f = st.back();
+            if (f.state == 0) {
+                Node nd;
+                init_node(nd, f.l, f.r);
+                const int count = f.r - f.l + 1;
+                if (count <= leaf_n) {
+                    nd.n = count;
+                    nd.index = f.l;
+                    out[f.me] = nd;
+                    st.pop_back();
+                    continue;
+                }
+                f.split = split_node(nd, f.l, f.r);
+                f.state = 1;
+                out[f.me] = nd;
+                if (f.l <= f.split) {                                  // left child = the next node in preorder
+                    const size_t c = out.size();
+                    out[f.me].left = base + (int)(c - root);
+                    out.push_back(Node());
+                    const Frame child{c, f.l, f.split, 0, 0};
+                    st.push_back(child);                               // invalidates f
+                }
+            } else if (f.state == 1) {
+                f.state = 2;
+                if (f.split + 1 <= f.r) {
+                    const size_t c = out.size();
+                    out[f.me].right = base + (int)(c - root);
+                    out.push_back(Node());
+                    const Frame child{c, f.split + 1, f.r, 0, 0};
+                    st.push_back(child);
+                }
+            } else {
+                st.pop_back();
+            }
         }
-        int split;
-        if (sah) split = sah_split(l, r);
-        else {
-            float lenx = nd.BB.x - nd.AA.x, leny = nd.BB.y - nd.AA.y, lenz = nd.BB.z - nd.AA.z;
-            // three independent ifs, not else-ifs (M:412-420): ties sort more than once
-            if (lenx >= leny && lenx >= lenz) sort_axis(recs + l, recs + r + 1, 0);
-            if (leny >= lenx && leny >= lenz) sort_axis(recs + l, recs + r + 1, 1);
-            if (lenz >= lenx && lenz >= leny) sort_axis(recs + l, recs + r + 1, 2);
-            split = (l + r) / 2;
-        }
-        if (task_cutoff > 0 && count > task_cutoff) {
-            // children as independent tasks into private arrays, then stitched in preorder
-            std::vector<Node> lsub, rsub;
-            #pragma omp task shared(lsub) firstprivate(l, split)
-            { build(lsub, 0, l, split); }
-            #pragma omp task shared(rsub) firstprivate(split, r)
-            { build(rsub, 0, split + 1, r); }
-            #pragma omp taskwait
-            const int lbase = base + 1, rbase = base + 1 + (int)lsub.size();
-            append_rebased(out, lsub, lbase);
-            append_rebased(out, rsub, rbase);
-            nd.left = lsub.empty() ? 0 : lbase;
-            nd.right = rsub.empty() ? 0 : rbase;
-        } else {
-            nd.left = build(out, base + 1, l, split);
-            const int used = (int)(out.size() - me);  // self + left subtree
-            nd.right = build(out, base + used, split + 1, r);
-        }
-        out[me] = nd;
-        return base;
     }
 
     static void append_rebased(std::vector<Node>& out, const std::vector<Node>& sub, int new_base) {
@@ -195,19 +213,87 @@ int build_bvh(std::vector<Tri>& tris, std::vector<Node>& nodes, int leaf_n, bool
     dummy.AA = V3{1, 1, 0}; dummy.BB = V3{0, 1, 0};
     nodes.push_back(dummy);
 
-    Builder b{recs.data(), leaf_n, sah, 0};
+    Builder b{recs.data(), leaf_n, sah};
+    bool done = false;
 #ifdef _OPENMP
     if (n_threads > 1 && T > 4096) {
-        b.task_cutoff = std::max(2048, T / (8 * n_threads));
+        // Ranges larger than `cutoff` ("big" nodes) are split by ONE thread walking the top of the tree in preorder with
+        // an explicit stack — each level needs the previous level's sort order, there is nothing to parallelise on that
+        // spine — and every range at or below the cutoff becomes a task that builds its subtree into a private array.
+        // The arrays are stitched in preorder afterwards.
+        const int cutoff = std::max(2048, T / (8 * n_threads));
+        struct Big { Node nd; int child[2]; bool child_is_job[2]; };
+        std::vector<Big> bigs;
+        std::deque<std::vector<Node>> jobs;                              // deque: references stay valid while tasks run
+        struct Walk { int big, l, r, split, state; };
         #pragma omp parallel num_threads(n_threads)
         #pragma omp single
-        { b.build(nodes, 1, 0, T - 1); }
-    } else
-#endif
-    {
-        (void)n_threads;
-        b.build(nodes, 1, 0, T - 1);
+        {
+            std::vector<Walk> st;
+            // returns (index, is_job) of the node built over [l, r]; big nodes are pushed onto the walk stack
+            auto open_range = [&](int l, int r, int& idx, bool& is_job) {
+                if (r - l + 1 <= cutoff) {
+                    jobs.emplace_back();
+                    std::vector<Node>* dst = &jobs.back();
+                    idx = (int)jobs.size() - 1; is_job = true;
+                    Builder* bp = &b;
+                    #pragma omp task firstprivate(dst, bp, l, r)
+                    { bp->build_seq(*dst, 0, l, r); }
+                } else {
+                    Big g;
+                    b.init_node(g.nd, l, r);
+                    g.child[0] = g.child[1] = -1; g.child_is_job[0] = g.child_is_job[1] = false;
+                    const int split = b.split_node(g.nd, l, r);
+                    bigs.push_back(g);
+                    idx = (int)bigs.size() - 1; is_job = false;
+                    st.push_back(Walk{idx, l, r, split, 0});
+                }
+            };
+            int root_idx; bool root_job;
+            open_range(0, T - 1, root_idx, root_job);
+            while (!st.empty()) {
+                Walk w = st.back();
+                if (w.state == 2) { st.pop_back(); continue; }
+                st.back().state = w.state + 1;
+                const int lo = w.state == 0 ? w.l : w.split + 1, hi = w.state == 0 ? w.split : w.r;
+                if (lo > hi) continue;
+                int idx; bool is_job;
+                open_range(lo, hi, idx, is_job);                        // may grow `bigs` and `st`
+                bigs[w.big].child[w.state] = idx;
+                bigs[w.big].child_is_job[w.state] = is_job;
+            }
+            #pragma omp taskwait
+            // stitch in preorder: id of a node = its position in `nodes` (the dummy is 0, the root 1)
+            if (root_job) {
+                Builder::append_rebased(nodes, jobs[root_idx], 1);
+            } else {
+                struct Emit { int big; int at; int state; };
+                std::vector<Emit> es;
+                es.push_back(Emit{root_idx, (int)nodes.size(), 0});
+                nodes.push_back(bigs[root_idx].nd);
+                while (!es.empty()) {
+                    Emit e = es.back();
+                    if (e.state == 2) { es.pop_back(); continue; }
+                    es.back().state = e.state + 1;
+                    const Big& g = bigs[e.big];
+                    const int c = g.child[e.state];
+                    if (c < 0) continue;
+                    const int id = (int)nodes.size();
+                    if (e.state == 0) nodes[e.at].left = id; else nodes[e.at].right = id;
+                    if (g.child_is_job[e.state]) {
+                        Builder::append_rebased(nodes, jobs[c], id);
+                    } else {
+                        nodes.push_back(bigs[c].nd);
+                        es.push_back(Emit{c, id, 0});
+                    }
+                }
+            }
+        }
+        done = true;
     }
+#endif
+    (void)n_threads;
+    if (!done) b.build_seq(nodes, 1, 0, T - 1);
 
     // gather the triangles into their final order (the reference moved them during every sort)
     std::vector<Tri> sorted((size_t)T);
