@@ -57,7 +57,9 @@ def build_scene(force=False):
 def build_pt(force=False):
     os.makedirs(BUILD, exist_ok=True)
     hdrs = [os.path.join(CSRC, h) for h in CUDA_HDRS] + [os.path.join(ROOT, "include", "pt.h"), os.path.join(ROOT, "include", "ptmath.h")]
-    units = [("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", []), ("pt_api", [])]
+    # production TU: approximate division / square root in SHADING (plain operators) — ray generation, ray/box/triangle
+    # tests, RNG, texel addressing and accumulation use the _rn intrinsics, which these flags do not touch; no -ftz.
+    units = [("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", ["-prec-div=false", "-prec-sqrt=false"]), ("pt_api", [])]
     objs = []
     for name, extra in units:
         src = os.path.join(CSRC, name + ".cu")

@@ -540,7 +540,7 @@ __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
 
 #define PT_PERSIST_CHUNK 1              // (tile, frame) items claimed per atomic
 #ifndef PT_PERSIST_MIN_CTAS
-#define PT_PERSIST_MIN_CTAS 6           // measured on B200 (is-1M / lambert-100k / disney-1M, Grays/s): 3 CTAs 11.6/5.7/5.3, 4: 12.4/6.5/6.1, 6: 12.6/7.0/6.8, 8: 12.1/6.9/6.7
+#define PT_PERSIST_MIN_CTAS 5           // measured on B200 (is-1M / lambert-100k / disney-1M, Grays/s): 3 CTAs 11.6/5.7/5.3, 4: 12.4/6.5/6.1, 6: 12.6/7.0/6.8, 8: 12.1/6.9/6.7
 #endif
 template <class Cfg, int VARIANT>
 __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(const __grid_constant__ RenderParams p) {
