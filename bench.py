@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="is-1M-1080p", choices=sorted(WORKLOADS))
-    ap.add_argument("--spp", type=int, default=64, help="frames (samples per pixel) per step")
+    ap.add_argument("--spp", type=int, default=256, help="frames (samples per pixel) per step")
     ap.add_argument("--pipeline", type=int, default=2, help="0 megakernel, 1 wavefront, 2 persistent (production)")
     ap.add_argument("--split", default="tile", choices=["tile", "sample"])
     ap.add_argument("--mode", type=int, default=0, help="0 fast (production), 1 parity-ref, 2 parity-wide")
@@ -119,6 +119,25 @@ def crop_region(W, H, frac=4):
     cw, ch = max(8, W // frac), max(8, H // frac)
     x0, y0 = (W - cw) // 2, (H - ch) // 2
     return x0, y0, x0 + cw, y0 + ch
+
+
+def basic_tracer_baseline():
+    """The reference's CPU tracer (BasicRayTracingWithC++/main.cpp compiled by oracle/build_ref.py with g++ -O3 -fopenmp,
+    SAMPLE = 200: BASELINE.json config 1), wall-clock on this box's host cores.  None if oracle/_ref was not built."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "basic_tracer_200spp")
+    if not os.path.exists(exe):
+        return None
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        t0 = time.perf_counter()
+        r = subprocess.run([exe], cwd=tmp, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+        dt = time.perf_counter() - t0
+        ok = r.returncode == 0 and os.path.exists(os.path.join(tmp, "basic_ray_tracing_with_c++.png"))
+    if not ok:
+        return None
+    return {"value": 256 * 256 * 200 / dt / 1e6, "unit": "Mpaths/s", "seconds": dt, "cores": os.cpu_count(), "kind": "reference",
+            "sample": "BasicRayTracingWithC++/main.cpp unmodified but SAMPLE=200, 256x256 Cornell box, 50 OpenMP threads as the "
+                      "source requests, wall clock incl. PNG write"}
 
 
 def algorithmic_bytes(c):
@@ -348,6 +367,9 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": cpu_rays / dt / 1e6, "unit": "Mrays/s", "cores": O.num_threads(), "kind": "port",
                                     "sample": "oracle (-O2 -fopenmp), centre crop %dx%d of %dx%d, 2 frames"
                                               % (reg[2] - reg[0], reg[3] - reg[1], W, H)}
+            basic = basic_tracer_baseline()
+            if basic is not None:
+                line["cpu_baseline_basic"] = basic
         print(json.dumps(line), flush=True)
     pt.close()
     if world > 1:

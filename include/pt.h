@@ -132,6 +132,10 @@ int pt_clear(pt_ctx* ctx);
 
 /* New (the reference never reads pixels back): W*H float4, row 0 = bottom row (GL window origin). Synchronises. */
 int pt_readback(pt_ctx* ctx, float* rgba, size_t bytes);
+/* pass3.draw() (M:706): the display pass pass3.fsh:14-24 — toneMapping(colour, 1.5) — fused with the window's 8-bit
+   conversion on the device; W*H RGBA8, row 0 = TOP row (image order), alpha 255.  A quarter of pt_readback's bytes
+   cross PCIe.  Synchronises. */
+int pt_readback_display(pt_ctx* ctx, unsigned char* rgba8, size_t bytes);
 /* Parity hook: triangle index (into the uploaded array) of the primary hit of the LAST frame rendered, -1 = miss. */
 int pt_readback_primary_ids(pt_ctx* ctx, int* ids, size_t bytes);
 

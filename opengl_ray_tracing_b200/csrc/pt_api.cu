@@ -59,6 +59,7 @@ struct pt_ctx {
     pt::WaveBuffers wf;          // wavefront path state, allocated at the first wavefront render
     void* wf_block = nullptr;
     uint32_t* sched = nullptr;   // persistent pipeline: work head + per-tile progress
+    uchar4* display = nullptr;   // pt_readback_display staging
     int num_sms = 0;
     // scene
     bool has_scene = false;
@@ -145,6 +146,24 @@ __global__ void k_rgb_to_float4(const float* __restrict__ src, size_t n, float4*
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     dst[i] = make_float4(src[3 * i], src[3 * i + 1], src[3 * i + 2], 0.f);
+}
+
+// pass3.fsh:14-24 — toneMapping(c, 1.5) = c * 1.0 / (1.0 + (0.3 r + 0.6 g + 0.1 b) / 1.5), then the window's 8-bit
+// UNORM conversion (round(clamp(v, 0, 1) * 255)).  Strict arithmetic: a float32 host restatement gives the same bytes.
+// Output rows run top to bottom (image order); the framebuffer's row 0 is the bottom row.
+__global__ void k_display(const float4* __restrict__ accum, int width, int height, uchar4* __restrict__ out) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= width || y >= height) return;
+    const float4 c = accum[(size_t)(height - 1 - y) * width + x];
+    const float lum = s_add(s_add(s_mul(0.3f, c.x), s_mul(0.6f, c.y)), s_mul(0.1f, c.z));
+    const float k = s_add(1.0f, s_div(lum, 1.5f));
+    float v[3] = {s_div(s_mul(c.x, 1.0f), k), s_div(s_mul(c.y, 1.0f), k), s_div(s_mul(c.z, 1.0f), k)};
+    unsigned char q[3];
+    for (int i = 0; i < 3; i++) {
+        float t = fminf(fmaxf(v[i], 0.0f), 1.0f);            // NaN -> 0
+        q[i] = (unsigned char)(int)s_add(s_mul(t, 255.0f), 0.5f);
+    }
+    out[(size_t)y * width + x] = make_uchar4(q[0], q[1], q[2], 255);
 }
 
 __global__ void k_scale(float4* __restrict__ a, size_t n, float s) {
@@ -298,7 +317,7 @@ int pt_destroy(pt_ctx* c) {
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->wf_block); cudaFree(c->sched); cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
+    cudaFree(c->wf_block); cudaFree(c->sched); cudaFree(c->display); cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -577,6 +596,21 @@ int pt_readback(pt_ctx* c, float* rgba, size_t bytes) {
     if (bytes < need) return fail(PT_EINVAL, "pt_readback: buffer too small");
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaMemcpyAsync(rgba, c->accum, need, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return collect_timing(c);
+}
+
+int pt_readback_display(pt_ctx* c, unsigned char* rgba8, size_t bytes) {
+    if (!c || !rgba8) return fail(PT_EINVAL, "pt_readback_display: null argument");
+    const size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    if (bytes < npx * 4) return fail(PT_EINVAL, "pt_readback_display: buffer too small");
+    CK(cudaSetDevice(c->cfg.device));
+    if (!c->display) CK(cudaMalloc(&c->display, npx * sizeof(uchar4)));
+    dim3 block(32, 8), grid((c->cfg.width + 31) / 32, (c->cfg.height + 7) / 8);
+    k_display<<<grid, block, 0, c->stream>>>(c->accum, c->cfg.width, c->cfg.height, c->display);
+    CK(cudaGetLastError());
+    c->launches += 1;
+    CK(cudaMemcpyAsync(rgba8, c->display, npx * 4, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return collect_timing(c);
 }

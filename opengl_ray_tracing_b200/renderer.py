@@ -23,7 +23,7 @@ DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 ACC_MEAN, ACC_SUM = 0, 1
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_render_spp", "pt_render_frames",
-           "pt_clear", "pt_readback", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
+           "pt_clear", "pt_readback", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
            "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_last_error",
            "pt_build_info"]
 
@@ -66,6 +66,7 @@ def lib():
         "pt_clear": (C.c_int, [vp]),
         "pt_readback": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_readback_primary_ids": (C.c_int, [vp, vp, C.c_size_t]),
+        "pt_readback_display": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_enable_cost_map": (C.c_int, [vp, C.c_int]),
         "pt_readback_cost_map": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_framebuffer_device_ptr": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
@@ -160,6 +161,12 @@ class PathTracer:
 
     def readback_into(self, host_ptr, nbytes):
         _check(lib().pt_readback(self._h, host_ptr, nbytes), "pt_readback")
+
+    def readback_display(self) -> np.ndarray:
+        """pass3.fsh tone map + 8-bit conversion on the device: uint8 [H, W, 4], row 0 = top row."""
+        out = np.empty((self.height, self.width, 4), np.uint8)
+        _check(lib().pt_readback_display(self._h, out.ctypes.data, out.nbytes), "pt_readback_display")
+        return out
 
     def readback_primary_ids(self) -> np.ndarray:
         out = np.empty((self.height, self.width), np.int32)

@@ -294,3 +294,23 @@ def test_wavefront_rejects_what_it_cannot_run(R):
         R.PathTracer(8, 8, 0, mode=R.MODE_PARITY_REF, pipeline=R.WAVEFRONT)
     with pytest.raises(R.PtError, match="max_bounce"):
         R.PathTracer(8, 8, 1, max_bounce=9, pipeline=R.WAVEFRONT)
+
+
+def test_display_pass_matches_pass3(R):
+    """pt_readback_display = pass3.fsh's toneMapping(c, 1.5) + UNORM8, restated in float32 numpy: identical bytes."""
+    sc = small_scene("is", "1k")
+    W, H = 70, 44
+    pt = R.PathTracer(W, H, sc.variant, mode=R.MODE_FAST)
+    pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); pt.set_camera(sc.eye, sc.cam)
+    pt.render_spp(0, 4)
+    img, disp = pt.readback(), pt.readback_display()
+    pt.close()
+    f = np.float32
+    c = img[::-1, :, :3].astype(f)
+    lum = (f(0.3) * c[..., 0] + f(0.6) * c[..., 1]) + f(0.1) * c[..., 2]
+    k = f(1.0) + lum / f(1.5)
+    v = np.clip((c * f(1.0)) / k[..., None], f(0), f(1))
+    want = (v * f(255.0) + f(0.5)).astype(np.int32).astype(np.uint8)
+    assert disp.shape == (H, W, 4) and (disp[..., 3] == 255).all()
+    assert (disp[..., :3] == want).all()
+    assert disp[..., :3].std() > 0
