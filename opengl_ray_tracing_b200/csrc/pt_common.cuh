@@ -38,6 +38,7 @@ __device__ __forceinline__ float s_sub(float a, float b) { return __fsub_rn(a, b
 __device__ __forceinline__ float s_mul(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float s_div(float a, float b) { return __fdiv_rn(a, b); }
 __device__ __forceinline__ float s_sqrt(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ float s_rcp(float a) { return __frcp_rn(a); }      // == s_div(1.0f, a): both correctly rounded
 __device__ __forceinline__ V3 s_sub3(V3 a, V3 b) { return mk3(s_sub(a.x, b.x), s_sub(a.y, b.y), s_sub(a.z, b.z)); }
 __device__ __forceinline__ float s_dot(V3 a, V3 b) {
     return s_add(s_add(s_mul(a.x, b.x), s_mul(a.y, b.y)), s_mul(a.z, b.z));
@@ -47,7 +48,7 @@ __device__ __forceinline__ V3 s_cross(V3 a, V3 b) {
                s_sub(s_mul(a.x, b.y), s_mul(b.x, a.y)));
 }
 __device__ __forceinline__ V3 s_normalize(V3 v) {
-    float k = s_div(1.0f, s_sqrt(s_dot(v, v)));
+    float k = s_rcp(s_sqrt(s_dot(v, v)));
     return mk3(s_mul(v.x, k), s_mul(v.y, k), s_mul(v.z, k));
 }
 // S + d*t

@@ -596,9 +596,9 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
                     p.cost[idx] = f == 0 ? dt : p.cost[idx] + dt;
                 }
             }
-            // publish: the warp barrier orders every lane's store before lane 0's fence, whose release is cumulative
+            // publish: the warp barrier orders every lane's store before lane 0's release store, and release is cumulative
             __syncwarp();
-            if (lane == 0) { __threadfence(); st_release_u32(progress + tile, f + 1); }
+            if (lane == 0) st_release_u32(progress + tile, f + 1);
         }
     }
     for (int o = 16; o > 0; o >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o);

@@ -24,7 +24,7 @@ struct Ray {
 };
 __device__ __forceinline__ Ray make_ray(V3 o, V3 d) {
     Ray r; r.o = o; r.d = d;
-    r.inv = mk3(s_div(1.0f, d.x), s_div(1.0f, d.y), s_div(1.0f, d.z));
+    r.inv = mk3(s_rcp(d.x), s_rcp(d.y), s_rcp(d.z));
     return r;
 }
 
@@ -68,6 +68,19 @@ __device__ __forceinline__ bool hit_triangle(const Ray& r, V3 p1, V3 p2, V3 p3, 
     t_out = t;
     inside = Nd > 0.0f;
     return true;
+}
+
+// The culling form of the slab test, for the padded boxes of the production tree: same products and the same
+// NaN-dropping min/max nesting as hit_aabb, but only the decision "hitAABB(...) > 0 and entry <= cull" is formed:
+//   hitAABB > 0  <=>  t1 >= t0 and t1 > 0   (t0 > 0 implies t1 > 0; otherwise the returned value is t1)
+__device__ __forceinline__ bool slab_cull(const Ray& r, V3 AA, V3 BB, float cull, float& entry) {
+    float fx = s_mul(s_sub(BB.x, r.o.x), r.inv.x), nx = s_mul(s_sub(AA.x, r.o.x), r.inv.x);
+    float fy = s_mul(s_sub(BB.y, r.o.y), r.inv.y), ny = s_mul(s_sub(AA.y, r.o.y), r.inv.y);
+    float fz = s_mul(s_sub(BB.z, r.o.z), r.inv.z), nz = s_mul(s_sub(AA.z, r.o.z), r.inv.z);
+    float t1 = fminf(fmaxf(fx, nx), fminf(fmaxf(fy, ny), fmaxf(fz, nz)));
+    float t0 = fmaxf(fminf(fx, nx), fmaxf(fminf(fy, ny), fminf(fz, nz)));
+    entry = fmaxf(t0, 0.0f);
+    return (t1 >= t0) && (t1 > 0.0f) && (entry <= cull);
 }
 
 struct TraceResult {
@@ -269,10 +282,9 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
             const float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
             cnt.inner();
             float e1, e2;
-            const float d1 = hit_aabb(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), e1);
-            const float d2 = hit_aabb(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), e2);
+            const bool g1 = slab_cull(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), cull, e1);
+            const bool g2 = slab_cull(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), cull, e2);
             const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
-            const bool g1 = (d1 > 0.0f) && (e1 <= cull), g2 = (d2 > 0.0f) && (e2 <= cull);
             if (g1 && g2) {
                 const bool left_first = e1 <= e2;
                 if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; return res; }
