@@ -13,6 +13,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -463,6 +464,29 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         s.root_ref = rn > 0 ? pt::ref_pack((uint32_t)rindex, (uint32_t)rn) : pt::ref_pack(0u, 0u);
         c->has_scene = true;
         c->launches += 5 + (hdrCache ? 1 : 0);
+        // Optional L2 persistence window over the production tree's nodes (north star item 2); PT_L2_WINDOW_MB=0 (default)
+        // leaves L2 to its own replacement: measured no gain, DESIGN.md §7.
+        if (const char* e = std::getenv("PT_L2_WINDOW_MB")) {
+            const size_t want = (size_t)std::atoi(e) << 20;
+            if (want > 0 && nFastInner > 0) {
+                cudaDeviceProp prop;
+                if (cudaGetDeviceProperties(&prop, c->cfg.device) == cudaSuccess && prop.accessPolicyMaxWindowSize > 0) {
+                    size_t bytes = (size_t)nFastInner * 64;
+                    if (bytes > want) bytes = want;
+                    if (bytes > (size_t)prop.accessPolicyMaxWindowSize) bytes = (size_t)prop.accessPolicyMaxWindowSize;
+                    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes);
+                    cudaStreamAttrValue attr;
+                    std::memset(&attr, 0, sizeof attr);
+                    attr.accessPolicyWindow.base_ptr = (void*)c->wnodes_fast;
+                    attr.accessPolicyWindow.num_bytes = bytes;
+                    attr.accessPolicyWindow.hitRatio = 1.0f;
+                    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                    cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &attr);
+                    cudaGetLastError();
+                }
+            }
+        }
     }
 done:
     cudaFree(d_order); cudaFree(d_leaf);
