@@ -37,7 +37,7 @@ WORKLOADS = {
     "is-1M-1080p": ("is", "1M", 1920, 1080, (2048, 1024)),          # BASELINE.json config 4 = the metric scene
     "disney-1M-1080p": ("disney", "1M", 1920, 1080, (1024, 512)),   # config 3
     "lambert-100k-1080p": ("lambert", "100k", 1920, 1080, (1024, 512)),  # config 2
-    "full-10M-4k": ("full", "10M", 3840, 2160, (2048, 1024)),       # config 5
+    "full-10M-4k": ("full", "10M", 3840, 2160, (2048, 1024)),       # config 5 (reference tree from buildBVH, see build_workload)
     "is-100k-1080p": ("is", "100k", 1920, 1080, (2048, 1024)),      # quick variant for development
     "is-10k-480p": ("is", "10k", 854, 480, (512, 256)),
 }
@@ -61,15 +61,45 @@ def parse_args():
 
 # ---------------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks/throttle reasons sampled every 50 ms while the timed region runs."""
+    """SM clock and throttle reasons of one GPU sampled every 5 ms through NVML while the timed region runs
+    (nvidia-smi -lms as the fallback when the NVML binding is missing)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, device_index):
         super().__init__(daemon=True)
-        self.idx, self.rows, self.proc = device_index, [], None
+        self.idx, self.rows, self.proc, self.halt = device_index, [], None, threading.Event()
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # LOCAL_RANK indexes CUDA_VISIBLE_DEVICES when it is set
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[device_index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else device_index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
 
     def run(self):
+        if self.nvml is not None:
+            n = self.nvml
+            bits = [getattr(n, "nvmlClocksEventReasonHwSlowdown", 0x8), getattr(n, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                    getattr(n, "nvmlClocksEventReasonSwThermalSlowdown", 0x20), getattr(n, "nvmlClocksEventReasonSwPowerCap", 0x4)]
+            while not self.halt.is_set():
+                try:
+                    sm = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+                    try:
+                        mask = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                    except Exception:
+                        mask = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                    self.rows.append([str(sm), str(self.max_sm), "0"] + ["Active" if mask & b else "Not Active" for b in bits])
+                except Exception:
+                    pass
+                self.halt.wait(0.005)
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "50"],
@@ -80,22 +110,23 @@ class ClockSampler(threading.Thread):
             pass
 
     def stop(self):
+        self.halt.set()
         if self.proc:
             self.proc.terminate()
         self.join(timeout=2)
         sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
-                for n, v in zip(names, r[3:7]):
+                for n, v in zip(self.NAMES, r[3:7]):
                     if v.lower().startswith("active"):
                         reasons.add(n)
             except (ValueError, IndexError):
                 continue
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm),
+                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def load_peaks():
@@ -110,7 +141,9 @@ def build_workload(name):
     from opengl_ray_tracing_b200 import scenes
     kind, size, W, H, hdr_res = WORKLOADS[name]
     t0 = time.time()
-    sc = scenes.build(kind, size, hdr_res=hdr_res)
+    # 10 M triangles: the exact restatement of buildBVHwithSAH needs hours of host time (O(n log^2 n) with the reference's
+    # tie order); the reference's other builder, buildBVH (M:787, commented alternative), takes 20 s and is used instead
+    sc = scenes.build(kind, size, hdr_res=hdr_res, builder="median" if size == "10M" else "sah")
     return sc, W, H, time.time() - t0
 
 
@@ -219,7 +252,12 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # the host BVH build (the reference's SAH builder, all cores) runs once: rank 0 builds and caches, the others load
+    if world > 1 and rank != 0:
+        dist.barrier()
     sc, W, H, t_scene = build_workload(args.workload)
+    if world > 1 and rank == 0:
+        dist.barrier()
 
     pt = R.PathTracer(W, H, sc.variant, device=local, mode=args.mode, pipeline=args.pipeline)
     t0 = time.perf_counter()
@@ -274,14 +312,21 @@ def run_ours(args):
     clocks = sampler.stop()
     st = pt.stats()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
-    tot = torch.tensor([dev_ms, float(st["rays"]), float(st["samples"]), float(st["launches"]), float(st["render_ms"])],
+    tot = torch.tensor([dev_ms, float(st["rays"]), float(st["samples"]), float(st["launches"]), float(st["render_ms"]),
+                        float(clocks["sm_mhz"] or 0.0), float(len(clocks["reasons"]))],
                        dtype=torch.float64, device="cuda")
     if world > 1:
         mx = tot.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         sm = tot.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         dev_ms, rays, samples, launches, kern_ms = float(mx[0]), float(sm[1]), float(sm[2]), float(sm[3]), float(mx[4])
+        allk = [torch.zeros_like(tot) for _ in range(world)]
+        dist.all_gather(allk, tot)
+        per_rank_kernel_ms = [float(t[4]) / args.steps for t in allk]
+        clocks["per_rank_sm_mhz"] = [float(t[5]) for t in allk]          # every rank samples its own GPU
+        clocks["ranks_with_reasons"] = int(sum(1 for t in allk if float(t[6]) > 0))
     else:
-        dev_ms, rays, samples, launches, kern_ms = [float(x) for x in tot]
+        dev_ms, rays, samples, launches, kern_ms = [float(x) for x in tot[:5]]
+        per_rank_kernel_ms = [kern_ms / args.steps]
     ms_per_step = dev_ms / args.steps
     mrays = rays / (dev_ms * 1e-3) / 1e6
     spp_per_s = samples / (W * H) / (dev_ms * 1e-3)
@@ -328,7 +373,7 @@ def run_ours(args):
                     "ms_per_step": t_e2e / args.steps * 1e3},
             "gpu_launches": int(launches), "clocks": clocks,
             "scene_build_s": t_scene, "scene_upload_s": t_upload, "wall_s_timed_region": t_wall,
-            "kernel_ms_per_step": kern_ms / args.steps,
+            "kernel_ms_per_step": kern_ms / args.steps, "per_rank_kernel_ms": per_rank_kernel_ms,
         }
         # roofline of the render kernel: algorithmic bytes from the kernel's OWN traversal counts (one frame of the
         # whole image through the counting build of the same kernel, outside the timed region), SURVEY.md §8(d)

@@ -60,6 +60,8 @@ struct pt_ctx {
     pt::WaveBuffers wf;          // wavefront path state, allocated at the first wavefront render
     void* wf_block = nullptr;
     uint32_t* sched = nullptr;   // persistent pipeline: work head + per-tile progress
+    float* sobol_tab = nullptr;  // variant 2: Sobol coordinates of the frames of one launch, [sobol_cap][8]
+    size_t sobol_cap = 0;
     uchar4* display = nullptr;   // pt_readback_display staging
     int num_sms = 0;
     // scene
@@ -74,7 +76,7 @@ struct pt_ctx {
     float eye[3] = {0, 0, 4};
     float cam[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 4, 1};
     int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
-    int band_world = 1, band_rank = 0;
+    int band_world = 1, band_rank = 0, band_diag = 0;
     // stats
     unsigned long long samples = 0, launches = 0;
     double render_ms = 0.0;
@@ -318,7 +320,7 @@ int pt_destroy(pt_ctx* c) {
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->wf_block); cudaFree(c->sched); cudaFree(c->display); cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
+    cudaFree(c->wf_block); cudaFree(c->sched); cudaFree(c->sobol_tab); cudaFree(c->display); cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -514,7 +516,14 @@ int pt_set_region(pt_ctx* c, int x0, int y0, int x1, int y1) {
 int pt_set_band_interleave(pt_ctx* c, int world, int rank) {
     if (!c) return fail(PT_EINVAL, "pt_set_band_interleave: null context");
     if (world < 1 || rank < 0 || rank >= world) return fail(PT_EINVAL, "pt_set_band_interleave: need 0 <= rank < world");
-    c->band_world = world; c->band_rank = rank;
+    c->band_world = world; c->band_rank = rank; c->band_diag = 0;
+    return PT_OK;
+}
+
+int pt_set_tile_interleave(pt_ctx* c, int world, int rank) {
+    if (!c) return fail(PT_EINVAL, "pt_set_tile_interleave: null context");
+    if (world < 1 || rank < 0 || rank >= world) return fail(PT_EINVAL, "pt_set_tile_interleave: need 0 <= rank < world");
+    c->band_world = world; c->band_rank = rank; c->band_diag = 1;
     return PT_OK;
 }
 
@@ -554,7 +563,7 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
     std::memcpy(p.cam, c->cam, 64);
     p.width = c->cfg.width; p.height = c->cfg.height;
     p.x0 = c->x0; p.y0 = c->y0; p.x1 = c->x1; p.y1 = c->y1;
-    p.band_world = c->band_world; p.band_rank = c->band_rank;
+    p.band_world = c->band_world; p.band_rank = c->band_rank; p.band_diag = c->band_diag;
     p.first_frame = first_frame; p.n_frames = n_frames; p.frame_stride = stride; p.accumulate_sum = accumulate;
     p.max_bounce = c->cfg.max_bounce;
     p.accum = c->accum; p.primary_ids = c->primary_ids; p.ray_counter = c->ray_counter; p.work_counters = c->ray_counter + 1; p.cost = c->cost;
@@ -569,10 +578,21 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
     }
     const bool persistent = c->cfg.pipeline == PT_PIPELINE_PERSISTENT;
     if (persistent && !c->sched) {
-        const size_t ntiles = (size_t)((c->cfg.width + 7) / 8) * (size_t)((c->cfg.height + 7) / 8) * 2;
+        const size_t ntiles = (size_t)((c->cfg.width + 7) / 8 + 64) * (size_t)((c->cfg.height + 7) / 8) * 2;   // 8x4 warp tiles (+ per-strip round-up of the diagonal split)
         CK(cudaMalloc(&c->sched, (64 + ntiles) * sizeof(uint32_t)));
     }
     p.sched = c->sched;
+    p.sobol_tab = nullptr;
+    if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS && !wavefront) {
+        if (c->sobol_cap < n_frames) {
+            CK(cudaStreamSynchronize(c->stream));            // an earlier launch may still read the old table
+            cudaFree(c->sobol_tab); c->sobol_tab = nullptr; c->sobol_cap = 0;
+            const size_t cap = std::max<size_t>(n_frames, 256);
+            CK(cudaMalloc(&c->sobol_tab, cap * 8 * sizeof(float)));
+            c->sobol_cap = cap;
+        }
+        p.sobol_tab = c->sobol_tab;
+    }
     CK(cudaEventRecord(c->ev0, c->stream));
     cudaError_t e;
     if (wavefront) {
@@ -594,13 +614,19 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
         const int mb = c->cfg.max_bounce;
         c->launches += (unsigned long long)n_frames * (1 + (mb + 1) + mb * (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS ? 2 : 1) + 1);
     } else {
-        c->launches += 1;
+        c->launches += p.sobol_tab ? 2 : 1;                  // the render kernel (+ the Sobol tabulation)
     }
     {
-        unsigned long long rows = 0;
-        for (int y = c->y0, b = 0; y < c->y1; y += 8, b++)
-            if (b % c->band_world == c->band_rank) rows += (unsigned long long)((c->y1 - y) < 8 ? (c->y1 - y) : 8);
-        c->samples += (unsigned long long)(c->x1 - c->x0) * rows * n_frames;
+        const pt::TileMap tm = pt::make_tile_map(c->x0, c->y0, c->x1, c->y1, c->band_world, c->band_rank, c->band_diag);
+        unsigned long long px = 0;
+        for (uint32_t t = 0; t < tm.count(); t++) {
+            int tx, strip;
+            tm.locate(t, tx, strip);
+            const int xa = c->x0 + tx * 8, ya = c->y0 + strip * 4;
+            const int w = std::min(c->x1, xa + 8) - xa, h = std::min(c->y1, ya + 4) - ya;
+            if (w > 0 && h > 0) px += (unsigned long long)w * h;
+        }
+        c->samples += px * n_frames;
     }
     return PT_OK;
 }

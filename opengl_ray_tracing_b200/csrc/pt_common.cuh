@@ -117,7 +117,8 @@ struct RenderParams {
     float cam[16];              // column-major cameraRotate
     int width, height;
     int x0, y0, x1, y1;         // region
-    int band_world, band_rank;  // interleaved 8-row bands: this launch owns band b iff b % band_world == band_rank
+    int band_world, band_rank;  // multi-GPU tile split, see TileMap
+    int band_diag;              // 0: whole 8-row bands, b % world == rank; 1: 8x4 tiles, (tx + strip) % world == rank
     unsigned first_frame, n_frames, frame_stride;
     int accumulate_sum;         // 0: running mean (P:869), 1: += colour
     int max_bounce;
@@ -126,9 +127,34 @@ struct RenderParams {
     unsigned long long* ray_counter;
     unsigned long long* work_counters;   // [4]: inner nodes fetched, triangles tested, leaf-box candidates, - (PT_MODE_FAST_COUNT)
     WaveBuffers wf;             // PT_PIPELINE_WAVEFRONT only
+    const float* sobol_tab;     // variant 2: [n_frames][8] Sobol coordinates of this launch's frames (written by sobol_table_kernel) or null
     uint32_t* sched;            // PT_PIPELINE_PERSISTENT: [0] work head, [64 + tile] next frame allowed to accumulate
     unsigned* cost;             // optional W*H cost map (SM cycles spent on the pixel by the last launch) or null
 };
+
+// Multi-GPU tile split: which 8x4 pixel warp tiles (tx = column, strip = 4-row strip, both counted from the region's
+// corner) a launch owns, and how the owned ones are numbered 0 .. rows * per_row - 1.
+//   bands    (pt_set_band_interleave): every tile of the 8-row band b = strip / 2 iff b % world == rank
+//   diagonal (pt_set_tile_interleave): tile (tx, strip) iff (tx + strip) % world == rank — every rank gets an even sample
+//            of the whole image (measured at 8 GPUs: slowest/mean rank 1.06 with bands)
+// A numbered tile can lie right of the region when the column count does not divide; its pixels fail the x1 test.
+struct TileMap {
+    int per_row, rows, world, rank, diag;
+    __host__ __device__ uint32_t count() const { return (uint32_t)per_row * (uint32_t)rows; }
+    __host__ __device__ void locate(uint32_t t, int& tx, int& strip) const {
+        const int row = (int)(t / (uint32_t)per_row), j = (int)(t - (uint32_t)row * (uint32_t)per_row);
+        if (diag) { strip = row; tx = ((rank - strip) % world + world) % world + j * world; }
+        else { strip = ((row >> 1) * world + rank) * 2 + (row & 1); tx = j; }
+    }
+};
+__host__ __device__ inline TileMap make_tile_map(int x0, int y0, int x1, int y1, int world, int rank, int diag) {
+    const int ntx = (x1 - x0 + 7) >> 3, strips = (y1 - y0 + 3) >> 2, bands = (y1 - y0 + 7) >> 3;
+    TileMap m;
+    m.world = world; m.rank = rank; m.diag = diag && world > 1;
+    if (m.diag) { m.per_row = (ntx + world - 1) / world; m.rows = strips; }
+    else { m.per_row = ntx; m.rows = 2 * (bands > rank ? (bands - rank + world - 1) / world : 0); }
+    return m;
+}
 
 struct Material {               // P:41-56 without the two fields no shader reads (IOR, transmission)
     V3 emissive, baseColor;

@@ -88,6 +88,25 @@ __device__ __forceinline__ float sobol(uint32_t d, uint32_t i) {
         if (i & 1u) result ^= c_sobol_v[j + offset];
     return s_mul(__uint2float_rn(result), 2.3283064365386963e-10f);          // 1.0f/float(0xFFFFFFFFU) == 2^-32
 }
+// The Sobol point of a frame is the same for every pixel (P:795-799: index = frameCounter + 1; the per-pixel part is the
+// Cranley-Patterson shift), and the loop above runs once per set bit POSITION of the frame index — 13 rounds at frame
+// 5000.  One tiny launch tabulates the 8 coordinates of each frame of a render launch with the very same function.
+static __global__ void sobol_table_kernel(float* __restrict__ tab, uint32_t first_frame, uint32_t n_frames, uint32_t stride) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_frames * 8u) return;
+    const uint32_t frame = first_frame + (i >> 3) * stride;
+    tab[i] = sobol(i & 7u, (frame + 1u) ^ ((frame + 1u) >> 1));
+}
+// row = the frame's 8 tabulated coordinates, or null: compute them here
+__device__ __forceinline__ void sobol_pair(const float* __restrict__ row, uint32_t bounce, uint32_t frame, float& u, float& v) {
+    if (row != nullptr && bounce < 4u) {
+        const float2 t = __ldg(reinterpret_cast<const float2*>(row) + bounce);
+        u = t.x; v = t.y;
+    } else {
+        u = sobol(bounce * 2u, (frame + 1u) ^ ((frame + 1u) >> 1));
+        v = sobol(bounce * 2u + 1u, (frame + 1u) ^ ((frame + 1u) >> 1));
+    }
+}
 __device__ __forceinline__ void cranley_patterson(int px, int py, float& u, float& v) {
     uint32_t pseed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + (uint32_t)(114514 / 1919) * 26699u) | 1u;
     float a = rnd(pseed), b = rnd(pseed);
@@ -345,8 +364,8 @@ __device__ __forceinline__ void generate_ray(const RenderParams& p, int px, int 
 #define PT_PH_SHADOW 2
 
 template <class Cfg, int VARIANT>
-__device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py, uint32_t frame, int& primary_id,
-                                           uint32_t& nrays, Counter<Cfg::COUNT>& cnt) {
+__device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py, uint32_t frame, const float* __restrict__ sobol_row,
+                                           int& primary_id, uint32_t& nrays, Counter<Cfg::COUNT>& cnt) {
     typedef typename Cfg::M M;
     const DevScene& sc = p.sc;
     uint32_t seed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + frame * 26699u) | 1u;            // P:73-76
@@ -417,8 +436,8 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
                 ndl = dot(N, Ld);
                 const bool want_shadow = ndl > 0.0f;
                 // BRDF sampling driven by Sobol + Cranley-Patterson, P:795-816
-                float su = sobol((uint32_t)bounce * 2u, (frame + 1u) ^ ((frame + 1u) >> 1));
-                float sv = sobol((uint32_t)bounce * 2u + 1u, (frame + 1u) ^ ((frame + 1u) >> 1));
+                float su, sv;
+                sobol_pair(sobol_row, (uint32_t)bounce, frame, su, sv);
                 cranley_patterson(px, py, su, sv);
                 const float xi_3 = rnd(seed);
                 const V3 L = SampleBRDF<M>(su, sv, xi_3, V, N, mat);
@@ -481,14 +500,16 @@ __device__ __forceinline__ void flush_counts(Counter<true>& cnt, unsigned long l
 }
 
 // ---- render kernel: one thread per pixel, a warp covers an 8x4 pixel tile, frames looped in registers ----
-#define PT_TILE_W 32     // CTA tile: 4 x 2 warps of 8 x 4 pixels
-#define PT_TILE_H 8
 
 template <class Cfg, int VARIANT>
 __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ RenderParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int px = p.x0 + blockIdx.x * PT_TILE_W + (warp & 3) * 8 + (lane & 7);
-    const int py = p.y0 + (blockIdx.y * p.band_world + p.band_rank) * PT_TILE_H + (warp >> 2) * 4 + (lane >> 3);
+    const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
+    const uint32_t tile = blockIdx.x * 8u + (uint32_t)warp;          // one owned 8x4 tile per warp
+    int tx = 0, strip = 0;
+    if (tile < tm.count()) tm.locate(tile, tx, strip);
+    const int px = tile < tm.count() ? p.x0 + tx * 8 + (lane & 7) : p.x1;
+    const int py = p.y0 + strip * 4 + (lane >> 3);
     uint32_t nrays = 0;
     Counter<Cfg::COUNT> cnt;
     if (px < p.x1 && py < p.y1) {
@@ -498,7 +519,7 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
         const long long t_start = p.cost ? clock64() : 0;
         for (uint32_t f = 0; f < p.n_frames; f++) {
             const uint32_t frame = p.first_frame + f * p.frame_stride;
-            V3 c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays, cnt);
+            V3 c = shade_sample<Cfg, VARIANT>(p, px, py, frame, p.sobol_tab ? p.sobol_tab + (size_t)f * 8 : nullptr, primary, nrays, cnt);
             if (p.accumulate_sum) {
                 acc.x = s_add(acc.x, c.x); acc.y = s_add(acc.y, c.y); acc.z = s_add(acc.z, c.z);
             } else {
@@ -545,10 +566,8 @@ __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
 template <class Cfg, int VARIANT>
 __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(const __grid_constant__ RenderParams p) {
     const int lane = threadIdx.x & 31;
-    const int tiles_x = (p.x1 - p.x0 + 7) >> 3;
-    const int bands = (p.y1 - p.y0 + 7) >> 3;
-    const int owned = bands > p.band_rank ? (bands - p.band_rank + p.band_world - 1) / p.band_world : 0;
-    const uint32_t ntiles = (uint32_t)tiles_x * (uint32_t)owned * 2u;
+    const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
+    const uint32_t ntiles = tm.count();                // owned 8x4 warp tiles
     const uint32_t nitems = ntiles * p.n_frames;
     uint32_t* head = p.sched;                          // [0] = next item; progress starts 64 words in
     uint32_t* progress = p.sched + 64;
@@ -564,15 +583,16 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
 #pragma unroll 1
         for (uint32_t item = first_item; item < first_item + PT_PERSIST_CHUNK && item < nitems; item++) {
             const uint32_t f = item / ntiles, tile = item - f * ntiles;
-            const uint32_t strip = tile / (uint32_t)tiles_x, tx = tile - strip * (uint32_t)tiles_x;
-            const int px = p.x0 + (int)tx * 8 + (lane & 7);
-            const int py = p.y0 + ((int)(strip >> 1) * p.band_world + p.band_rank) * 8 + (int)(strip & 1u) * 4 + (lane >> 3);
+            int tx, strip;
+            tm.locate(tile, tx, strip);
+            const int px = p.x0 + tx * 8 + (lane & 7);
+            const int py = p.y0 + strip * 4 + (lane >> 3);
             const bool valid = px < p.x1 && py < p.y1;
             const uint32_t frame = p.first_frame + f * p.frame_stride;
             const long long t_start = p.cost ? clock64() : 0;
             V3 c = mk3(0, 0, 0);
             int primary = -1;
-            if (valid) c = shade_sample<Cfg, VARIANT>(p, px, py, frame, primary, nrays, cnt);
+            if (valid) c = shade_sample<Cfg, VARIANT>(p, px, py, frame, p.sobol_tab ? p.sobol_tab + (size_t)f * 8 : nullptr, primary, nrays, cnt);
             // ordered accumulation
             if (lane == 0) while (ld_acquire_u32(progress + tile) != f) __nanosleep(32);
             __syncwarp();
@@ -608,13 +628,13 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
 
 template <class Cfg>
 cudaError_t launch_persistent(const RenderParams& p, int variant, int num_sms, cudaStream_t stream) {
-    const int tiles_x = (p.x1 - p.x0 + 7) >> 3;
-    const int bands = (p.y1 - p.y0 + 7) >> 3;
-    const int owned = bands > p.band_rank ? (bands - p.band_rank + p.band_world - 1) / p.band_world : 0;
-    if (owned == 0) return cudaSuccess;
-    const size_t ntiles = (size_t)tiles_x * owned * 2;
+    const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
+    const size_t ntiles = tm.count();
+    if (ntiles == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(p.sched, 0, (64 + ntiles) * sizeof(uint32_t), stream);
     if (e != cudaSuccess) return e;
+    if (variant == 2 && p.sobol_tab)
+        sobol_table_kernel<<<(p.n_frames * 8 + 255) / 256, 256, 0, stream>>>(const_cast<float*>(p.sobol_tab), p.first_frame, p.n_frames, p.frame_stride);
     // one resident set of CTAs: SMs x (CTAs that fit per SM), never more warps than there are tiles
     void (*kern)(const RenderParams) = variant == 0 ? render_persistent<Cfg, 0> : variant == 1 ? render_persistent<Cfg, 1> : render_persistent<Cfg, 2>;
     int per_sm = 0;
@@ -629,10 +649,11 @@ cudaError_t launch_persistent(const RenderParams& p, int variant, int num_sms, c
 
 template <class Cfg>
 cudaError_t launch_render(const RenderParams& p, int variant, cudaStream_t stream) {
-    const int bands = (p.y1 - p.y0 + PT_TILE_H - 1) / PT_TILE_H;                     // 8-row bands in the region
-    const int owned = bands > p.band_rank ? (bands - p.band_rank + p.band_world - 1) / p.band_world : 0;
-    if (owned == 0) return cudaSuccess;
-    dim3 grid((p.x1 - p.x0 + PT_TILE_W - 1) / PT_TILE_W, owned), block(256);
+    const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
+    if (tm.count() == 0) return cudaSuccess;
+    dim3 grid((tm.count() + 7) / 8), block(256);                                     // one warp per owned 8x4 tile
+    if (variant == 2 && p.sobol_tab)
+        sobol_table_kernel<<<(p.n_frames * 8 + 255) / 256, 256, 0, stream>>>(const_cast<float*>(p.sobol_tab), p.first_frame, p.n_frames, p.frame_stride);
     if (variant == 0) render_kernel<Cfg, 0><<<grid, block, 0, stream>>>(p);
     else if (variant == 1) render_kernel<Cfg, 1><<<grid, block, 0, stream>>>(p);
     else render_kernel<Cfg, 2><<<grid, block, 0, stream>>>(p);

@@ -89,10 +89,8 @@ template <class Cfg, int VARIANT>
 __global__ void __launch_bounds__(256) wf_generate(const __grid_constant__ RenderParams p, uint32_t frame, int write_ids) {
     const WaveBuffers& wf = p.wf;
     const int lane = threadIdx.x & 31;
-    const int tiles_x = (p.x1 - p.x0 + 7) >> 3;
-    const int bands = (p.y1 - p.y0 + 7) >> 3;
-    const int owned = bands > p.band_rank ? (bands - p.band_rank + p.band_world - 1) / p.band_world : 0;
-    const uint32_t ntiles = (uint32_t)tiles_x * (uint32_t)owned * 2u;
+    const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
+    const uint32_t ntiles = tm.count();                // owned 8x4 warp tiles
     uint32_t nrays = 0;
     Counter<Cfg::COUNT> cnt;
     for (;;) {
@@ -102,10 +100,10 @@ __global__ void __launch_bounds__(256) wf_generate(const __grid_constant__ Rende
         for (uint32_t k = 0; k < PT_WF_CHUNK; k += 32) {
             const uint32_t tile = (base + k) >> 5;
             bool valid = tile < ntiles;
-            // tiles are numbered along x within a 4-row strip; strips go bottom-up through the owned 8-row bands
-            const uint32_t strip = valid ? tile / (uint32_t)tiles_x : 0u, tx = valid ? tile % (uint32_t)tiles_x : 0u;
-            const int px = p.x0 + (int)tx * 8 + (lane & 7);
-            const int py = p.y0 + ((int)(strip >> 1) * p.band_world + p.band_rank) * 8 + (int)(strip & 1u) * 4 + (lane >> 3);
+            int tx = 0, strip = 0;
+            if (valid) tm.locate(tile, tx, strip);                   // owned tiles as TileMap numbers them
+            const int px = p.x0 + tx * 8 + (lane & 7);
+            const int py = p.y0 + strip * 4 + (lane >> 3);
             valid = valid && px < p.x1 && py < p.y1;
             bool alive = false;
             const size_t idx = (size_t)py * p.width + px;

@@ -4,8 +4,8 @@ Every pixel and every frame index of the reference is independent (per-pixel see
 pass1.fsh:73-76; Sobol index = frame + 1, pass1.fsh:795), so the path shards with no data-path collective;
 the only exchange is combining the per-GPU fp32 framebuffers when an image is wanted:
 
-  tile split    rank r renders the interleaved horizontal bands b with b % world == r of ALL frames
-                (running mean, bit-identical to a single-GPU render); combine = sum of disjoint regions
+  tile split    rank r renders the 8x4 pixel tiles (tx, s) with (tx + s) % world == r (or whole 8-row bands with
+                b % world == r) of ALL frames (running mean, bit-identical to a single-GPU render); combine = sum of disjoint regions
                 (x + 0 is exact) with one NCCL reduce, or nothing at all if only rank-local tiles are needed.
   sample split  rank r renders frames first + r, first + r + world, … of ALL pixels as a plain sum; combine =
                 one NCCL reduce(sum) + a scale by 1/total_frames (fp32 sum order differs from the sequential
@@ -19,6 +19,7 @@ from __future__ import annotations
 from dataclasses import dataclass
 
 BAND_ROWS = 8      # one CTA tile row (PT_TILE_H): bands stay aligned to the kernel's 32x8 pixel tiles
+TILE_COLS, TILE_ROWS = 8, 4     # one warp's pixel tile: the unit of the diagonal split
 
 
 @dataclass(frozen=True)
@@ -28,6 +29,24 @@ class TilePlan:
     world: int
     rank: int
     band_rows: int = BAND_ROWS
+    layout: str = "diagonal"       # "diagonal": 8x4 tiles, (tx + strip) % world == rank; "bands": whole bands, b % world == rank
+
+    def tiles(self):
+        """[(x0, y0, x1, y1)] owned by this rank under the diagonal layout (pt_set_tile_interleave): 8x4 pixel tiles
+        (tx, strip) with (tx + strip) % world == rank — an even sample of the whole image for every rank."""
+        out = []
+        ns = (self.height + TILE_ROWS - 1) // TILE_ROWS
+        ntx = (self.width + TILE_COLS - 1) // TILE_COLS
+        for s in range(ns):
+            for tx in range((self.rank - s) % self.world, ntx, self.world):
+                out.append((tx * TILE_COLS, s * TILE_ROWS, min(self.width, (tx + 1) * TILE_COLS), min(self.height, (s + 1) * TILE_ROWS)))
+        return out
+
+    def rects(self):
+        """The owned pixel rectangles of the chosen layout."""
+        if self.layout == "bands":
+            return [(0, y0, self.width, y1) for y0, y1 in self.bands()]
+        return self.tiles()
 
     def bands(self):
         """[(y0, y1)] owned by this rank — interleaved so sky rows and geometry rows spread over all ranks."""
@@ -38,7 +57,7 @@ class TilePlan:
         return out
 
     def pixels(self):
-        return sum(y1 - y0 for y0, y1 in self.bands()) * self.width
+        return sum((x1 - x0) * (y1 - y0) for x0, y0, x1, y1 in self.rects())
 
 
 @dataclass(frozen=True)
@@ -53,14 +72,17 @@ class SamplePlan:
 
 
 def render_tiles(pt, plan: TilePlan, first_frame: int, n_frames: int):
-    """Tile-split render of frames [first_frame, first_frame+n_frames) on this rank's bands (running mean)."""
-    if hasattr(pt, "set_band_interleave"):          # the CUDA renderer does the interleave inside one launch
+    """Tile-split render of frames [first_frame, first_frame+n_frames) on this rank's tiles (running mean)."""
+    if hasattr(pt, "set_tile_interleave"):          # the CUDA renderer does the interleave inside one launch
         pt.set_region(0, 0, plan.width, plan.height)
-        pt.set_band_interleave(plan.world, plan.rank)
+        if plan.layout == "bands":
+            pt.set_band_interleave(plan.world, plan.rank)
+        else:
+            pt.set_tile_interleave(plan.world, plan.rank)
         pt.render_spp(first_frame, n_frames)
         return
-    for y0, y1 in plan.bands():                     # stand-in renderers (CPU tests): one call per band
-        pt.set_region(0, y0, plan.width, y1)
+    for x0, y0, x1, y1 in plan.rects():             # stand-in renderers (CPU tests): one call per rectangle
+        pt.set_region(x0, y0, x1, y1)
         pt.render_spp(first_frame, n_frames)
 
 

@@ -22,7 +22,7 @@ DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 
 ACC_MEAN, ACC_SUM = 0, 1
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
-EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_render_spp", "pt_render_frames",
+EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
            "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_last_error",
            "pt_build_info"]
@@ -61,6 +61,7 @@ def lib():
         "pt_set_camera": (C.c_int, [vp, f32p, f32p]),
         "pt_set_region": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int]),
         "pt_set_band_interleave": (C.c_int, [vp, C.c_int, C.c_int]),
+        "pt_set_tile_interleave": (C.c_int, [vp, C.c_int, C.c_int]),
         "pt_render_spp": (C.c_int, [vp, C.c_uint, C.c_uint]),
         "pt_render_frames": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_int]),
         "pt_clear": (C.c_int, [vp]),
@@ -137,6 +138,10 @@ class PathTracer:
     def set_band_interleave(self, world, rank):
         """This context renders 8-row band b iff b % world == rank (tile split in one launch)."""
         _check(lib().pt_set_band_interleave(self._h, world, rank), "pt_set_band_interleave")
+
+    def set_tile_interleave(self, world, rank):
+        """This context renders the 8x4 pixel tile (tx, strip) iff (tx + strip) % world == rank (tile split in one launch)."""
+        _check(lib().pt_set_tile_interleave(self._h, world, rank), "pt_set_tile_interleave")
 
     def render_spp(self, first_frame, n_frames):
         """frameCounter = first_frame .. first_frame+n_frames-1; asynchronous."""

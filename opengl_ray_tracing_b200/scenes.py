@@ -81,7 +81,7 @@ KINDS = {"lambert": (0, 2), "disney": (1, 5), "is": (2, 2), "full": (0, 2)}
 
 
 def build(kind: str, size: str = "10k", hdr_res=(1024, 512), hdr_path: str | None = None, threads: int | None = None,
-          camera=(0.0, 0.0, 4.0), use_cache: bool = True) -> BuiltScene:
+          camera=(0.0, 0.0, 4.0), use_cache: bool = True, builder: str = "sah") -> BuiltScene:
     """kind in KINDS; size in FREQ_FOR (per-mesh triangle count; 'full' has ten meshes of size/10… see below)."""
     variant, bounces = KINDS[kind]
     freq = FREQ_FOR[size] if isinstance(size, str) else int(size)
@@ -89,14 +89,19 @@ def build(kind: str, size: str = "10k", hdr_res=(1024, 512), hdr_path: str | Non
         freq = max(2, int(round(freq / np.sqrt(10.0))))          # ten meshes share the triangle budget
     threads = threads or min(16, os.cpu_count() or 1)
     os.makedirs(CACHE_DIR, exist_ok=True)
-    key = hashlib.sha1(("%s-%d-v3" % (kind, freq)).encode()).hexdigest()[:16]
+    # builder "sah" = buildBVHwithSAH (what the reference's main() calls, M:788); "median" = buildBVH, the alternative the
+    # reference keeps commented out one line above (M:787) — seconds instead of hours at 10 M triangles
+    key = hashlib.sha1(("%s-%d-v3%s" % (kind, freq, "" if builder == "sah" else "-" + builder)).encode()).hexdigest()[:16]
     path = os.path.join(CACHE_DIR, "%s_%d_%s.ptsc" % (kind, freq, key))
     sc = S.Scene()
     if use_cache and os.path.exists(path):
         sc.load(path)
     else:
         _populate(sc, kind, freq)
-        sc.buildBVHwithSAH(8, threads)                           # M:788
+        if builder == "sah":
+            sc.buildBVHwithSAH(8, threads)                       # M:788
+        else:
+            sc.buildBVH(8, threads)                              # M:787
         if use_cache:
             sc.save(path)
     tris, nodes = sc.triangles_encoded(), sc.nodes_encoded()

@@ -14,7 +14,7 @@ W, H, NF = 40, 28, 4
 
 
 class OracleRenderer:
-    """Same surface as renderer.PathTracer, minus set_band_interleave (so render_tiles issues one call per band)."""
+    """Same surface as renderer.PathTracer, minus set_tile_interleave (so render_tiles issues one call per rectangle)."""
 
     def __init__(self, sc):
         self.sc, self.width, self.height = sc, W, H
@@ -42,8 +42,8 @@ def _worker(rank, world, port, split, out_path):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     sc = small_scene("is", "1k")
     pt = OracleRenderer(sc)
-    if split == "tile":
-        D.render_tiles(pt, D.TilePlan(W, H, world, rank, band_rows=8), 0, NF)
+    if split.startswith("tile"):
+        D.render_tiles(pt, D.TilePlan(W, H, world, rank, band_rows=8, layout=split.split("-")[1]), 0, NF)
         out = D.combine(torch.from_numpy(pt.fb))
     else:
         D.render_samples(pt, D.SamplePlan(world, rank), 0, NF)
@@ -62,7 +62,7 @@ def _free_port():
     return p
 
 
-@pytest.mark.parametrize("split", ["tile", "sample"])
+@pytest.mark.parametrize("split", ["tile-diagonal", "tile-bands", "sample"])
 def test_two_ranks_match_one(tmp_path, split):
     import torch.multiprocessing as mp
     out_path = str(tmp_path / ("fb_%s.npy" % split))
@@ -70,7 +70,7 @@ def test_two_ranks_match_one(tmp_path, split):
     got = np.load(out_path)
     sc = small_scene("is", "1k")
     ref, _, _ = oracle_render(sc, W, H, 0, NF)
-    if split == "tile":
+    if split.startswith("tile"):
         assert got[..., :3].tobytes() == ref[..., :3].tobytes(), "tile split must be bit-identical to one renderer"
     else:
         assert rrmse(got, ref) < 1e-5          # same samples, different fp32 summation order
@@ -83,10 +83,20 @@ def test_plans_partition_the_work():
             for y0, y1 in D.TilePlan(1920, 1080, world, r).bands():
                 rows[y0:y1] += 1
         assert (rows == 1).all()
+        for (w, h) in ((1920, 1080), (854, 480), (33, 9)):          # diagonal 8x4 tiles cover every pixel exactly once
+            cover = np.zeros((h, w), int)
+            for r in range(world):
+                plan = D.TilePlan(w, h, world, r)
+                for x0, y0, x1, y1 in plan.tiles():
+                    cover[y0:y1, x0:x1] += 1
+                assert plan.pixels() == sum((x1 - x0) * (y1 - y0) for x0, y0, x1, y1 in plan.tiles())
+            assert (cover == 1).all()
         frames = []
         for r in range(world):
             first, count, stride = D.SamplePlan(world, r).frames(5, 13)
             frames += [first + k * stride for k in range(count)]
         assert sorted(frames) == list(range(5, 18))
-    px = [D.TilePlan(1920, 1080, 8, r).pixels() for r in range(8)]
+    px = [D.TilePlan(1920, 1080, 8, r, layout="bands").pixels() for r in range(8)]
     assert max(px) - min(px) <= 8 * 1920       # interleaving balances the bands
+    px = [D.TilePlan(1920, 1080, 8, r).pixels() for r in range(8)]
+    assert max(px) - min(px) <= 8 * 4 * 8      # ... and the diagonal tiles to within a few tiles

@@ -130,6 +130,21 @@ def test_regions_and_band_interleave_tile_the_image(R):
         q.set_band_interleave(3, rank); q.render_spp(0, NF)
         parts.append(q.readback()); q.close()
     assert (parts[0] + parts[1] + parts[2]).tobytes() == full.tobytes()      # disjoint: x + 0 is exact
+    from opengl_ray_tracing_b200 import dist as D
+    for world in (2, 5):                                     # diagonal 8x4 tiles: disjoint, complete, where TilePlan says
+        parts, px = [], 0
+        for rank in range(world):
+            q = R.PathTracer(W, H, sc.variant, mode=R.MODE_FAST)
+            q.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); q.set_camera(sc.eye, sc.cam)
+            q.set_tile_interleave(world, rank); q.render_spp(0, NF)
+            img = q.readback(); px += q.stats()["samples"]; q.close()
+            own = np.zeros((H, W), bool)
+            for x0, y0, x1, y1 in D.TilePlan(W, H, world, rank).tiles():
+                own[y0:y1, x0:x1] = True
+            assert (img[~own] == 0).all() and (img[own][:, 3] == 1).all()
+            parts.append(img)
+        assert sum(parts[1:], parts[0]).tobytes() == full.tobytes()
+        assert px == W * H * NF
 
 
 def test_sample_split_sum_matches_running_mean(R):
@@ -238,6 +253,14 @@ def test_pipelines_continue_frames_split_regions_and_sum(R, pipeline):
         q = R.PathTracer(W, H, sc.variant, mode=R.MODE_PARITY_FAST, pipeline=pipeline)
         q.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); q.set_camera(sc.eye, sc.cam)
         q.set_band_interleave(3, rank); q.render_spp(0, NF)
+        parts.append(q.readback()); q.close()
+    assert (parts[0] + parts[1] + parts[2]).tobytes() == full.tobytes()
+    # interleaved 8x4 tiles over 3 ranks
+    parts = []
+    for rank in range(3):
+        q = R.PathTracer(W, H, sc.variant, mode=R.MODE_PARITY_FAST, pipeline=pipeline)
+        q.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); q.set_camera(sc.eye, sc.cam)
+        q.set_tile_interleave(3, rank); q.render_spp(0, NF)
         parts.append(q.readback()); q.close()
     assert (parts[0] + parts[1] + parts[2]).tobytes() == full.tobytes()
     # sample split: strided frames as plain sums
