@@ -97,10 +97,17 @@ int pt_destroy(pt_ctx* ctx);
    tris:  nTriangles x 36 floats, Triangle_encoded (M:50-60).
    nodes: nNodes x 12 floats, BVHNode_encoded (M:68-72); node 0 is the dummy, root is node 1 (M:780-788).
    hdr:   hdrH x hdrW x 3 floats, rows in file order (sampled NEAREST + CLAMP_TO_EDGE, M:185-195).
-   hdrCache: same shape, calculateHdrCache output (M:555-652); may be NULL for variants 0 and 1.
+   hdrCache: same shape, calculateHdrCache output (M:555-652); may be NULL: variants 0 and 1 do not read it, and for
+   variant 2 the table is then computed on the device (same arithmetic, same table: pt_calculate_hdr_cache).
    Validates the tree, then repacks on the device into the traversal layout (DESIGN.md "HBM layout"). */
 int pt_upload_scene(pt_ctx* ctx, const float* tris, int nTriangles, const float* nodes, int nNodes,
                     const float* hdr, const float* hdrCache, int hdrW, int hdrH);
+
+/* calculateHdrCache (M:555-652) on a CUDA device: hdr and cache are host arrays of height*width*3 floats, cache receives the
+   table (x/w, y/h, pdf) bit for bit as the reference's host loop produces it (its sequential fp32 sums are kept sequential,
+   the searches run in parallel).  Needs no context.  pt_upload_scene runs the same kernels when variant 2 is handed
+   hdrCache = NULL. */
+int pt_calculate_hdr_cache(int device, const float* hdr, int width, int height, float* cache);
 
 /* glUniform3fv(eye) + glUniformMatrix4fv(cameraRotate, GL_FALSE) (M:678-679): cameraRotate is column-major. */
 int pt_set_camera(pt_ctx* ctx, const float eye[3], const float cameraRotate[16]);

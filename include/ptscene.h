@@ -106,6 +106,9 @@ void pts_free(void* p);
 /* pass3.fsh:14-24 tone map c/(1+lum/1.5) and a PPM/PFM writer for headless output */
 int pts_write_pfm(const char* path, const float* rgba, int width, int height);
 int pts_write_ppm_tonemapped(const char* path, const float* rgba, int width, int height);
+/* 8-bit PNG (stored deflate blocks, what svpng of Basic/main.cpp:169-190 produces): rows top first, 3 or 4 channels.
+   Feed it pt_readback_display's bytes to get the image the reference's window shows. */
+int pts_write_png(const char* path, const unsigned char* pixels, int width, int height, int channels);
 
 const char* pts_last_error(void);
 

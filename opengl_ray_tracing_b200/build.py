@@ -2,6 +2,7 @@
 
     libptscene.so   host scene library            (g++, csrc/scene/*.cpp)
     libpt.so        CUDA path tracer, C ABI       (nvcc -gencode arch=compute_100a,code=sm_100a)
+    ptdrive         headless C++ driver: the reference's main()/display() over the two C ABIs (g++, csrc/ptdrive.cpp)
 
 The built .so files are git-ignored but travel to the GPU box with the snapshot.  nvcc cross-compiles
 for sm_100a without a GPU.  Two translation units hold the render kernels because they need different
@@ -22,7 +23,7 @@ BUILD = os.path.join(HERE, "build")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 SCENE_SRC = ["pts_scene.cpp", "pts_bvh.cpp", "pts_hdr.cpp", "pts_meshgen.cpp"]
-CUDA_HDRS = ["pt_common.cuh", "pt_trace.cuh", "pt_shade.cuh", "pt_sobol_v.inc"]
+CUDA_HDRS = ["pt_common.cuh", "pt_trace.cuh", "pt_shade.cuh", "pt_wavefront.cuh", "pt_sobol_v.inc"]
 
 
 def _run(cmd, log=None):
@@ -59,7 +60,7 @@ def build_pt(force=False):
     hdrs = [os.path.join(CSRC, h) for h in CUDA_HDRS] + [os.path.join(ROOT, "include", "pt.h"), os.path.join(ROOT, "include", "ptmath.h")]
     # production TU: approximate division / square root in SHADING (plain operators) — ray generation, ray/box/triangle
     # tests, RNG, texel addressing and accumulation use the _rn intrinsics, which these flags do not touch; no -ftz.
-    units = [("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", ["-prec-div=false", "-prec-sqrt=false"]), ("pt_api", [])]
+    units = [("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", ["-prec-div=false", "-prec-sqrt=false"]), ("pt_api", []), ("pt_hdrcache", ["-fmad=false"])]
     objs = []
     for name, extra in units:
         src = os.path.join(CSRC, name + ".cu")
@@ -77,8 +78,18 @@ def build_pt(force=False):
     return out
 
 
+def build_drive(force=False):
+    src = os.path.join(CSRC, "ptdrive.cpp")
+    out = os.path.join(HERE, "ptdrive")
+    deps = [src, os.path.join(ROOT, "include", "pt.h"), os.path.join(ROOT, "include", "ptscene.h"),
+            os.path.join(HERE, "libpt.so"), os.path.join(HERE, "libptscene.so")]
+    if force or _stale(out, deps):
+        _run(["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", src, "-L", HERE, "-lpt", "-lptscene", "-Wl,-rpath,$ORIGIN", "-o", out])
+    return out
+
+
 def build_all(force=False):
-    return build_scene(force), build_pt(force)
+    return build_scene(force), build_pt(force), build_drive(force)
 
 
 if __name__ == "__main__":

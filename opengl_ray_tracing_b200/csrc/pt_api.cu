@@ -31,6 +31,7 @@ struct FastTree {
     uint32_t root_ref = 0; int depth = 0; int n_leaves = 0; float pad = 0.0f;
 };
 void build_fast_tree(const float* tris_raw, int nTriangles, const float* nodes_raw, int nNodes, FastTree& out, int threads);
+cudaError_t hdr_cache_device(const float* d_rgb, int W, int H, float4* d_cache4, float* d_cache3, cudaStream_t st);   // pt_hdrcache.cu
 cudaError_t launch_fast(const RenderParams& p, int variant, bool count, cudaStream_t stream);
 cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
 cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
@@ -334,8 +335,6 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     if (nTriangles <= 0 || nNodes < 2 || hdrW <= 0 || hdrH <= 0) return fail(PT_EINVAL, "pt_upload_scene: empty scene or HDR map");
     if (nTriangles >= (1 << 24) || nNodes >= (1 << 24))
         return fail(PT_ERANGE, "pt_upload_scene: index not exact in the reference's float encoding (>= 2^24)");
-    if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS && !hdrCache)
-        return fail(PT_EINVAL, "pt_upload_scene: variant 2 needs the hdrCache table (calculateHdrCache)");
     std::string why;
     int depth = validate_tree(nodes, nNodes, nTriangles, why);
     if (depth < 0) return fail(PT_EFORMAT, "pt_upload_scene: " + why);
@@ -376,7 +375,7 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     float* d_tmp = nullptr;
     void* d_scan = nullptr;
     size_t scan_bytes = 0;
-    int nInner = 0, nFastInner = 0, fast_depth = 0;
+    int nInner = 0, nFastInner = 0, fast_depth = 0, cache_launches = 0;
     uint32_t root_fast = 0;
     int rc = PT_OK;
 #define CKU(call)                                                                                  \
@@ -451,6 +450,11 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         CKU(cudaMemcpyAsync(d_tmp, hdrCache, ntex * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
         k_rgb_to_float4<<<(unsigned)((ntex + 255) / 256), 256, 0, st>>>(d_tmp, ntex, c->cache4);
         CKU(cudaGetLastError());
+    } else if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS) {
+        // no table supplied: calculateHdrCache (M:555-652) runs here on the device, same arithmetic, same table
+        CKU(cudaMalloc(&c->cache4, ntex * sizeof(float4)));
+        CKU(pt::hdr_cache_device(d_tmp, hdrW, hdrH, c->cache4, nullptr, st));
+        cache_launches = 6;
     }
     CKU(cudaStreamSynchronize(st));
     {
@@ -465,7 +469,7 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         int rn = (int)nodes[12 + 3], rindex = (int)nodes[12 + 4];
         s.root_ref = rn > 0 ? pt::ref_pack((uint32_t)rindex, (uint32_t)rn) : pt::ref_pack(0u, 0u);
         c->has_scene = true;
-        c->launches += 5 + (hdrCache ? 1 : 0);
+        c->launches += 5 + (hdrCache ? 1 : cache_launches);
         // Optional L2 persistence window over the production tree's nodes (north star item 2); PT_L2_WINDOW_MB=0 (default)
         // leaves L2 to its own replacement: measured no gain, DESIGN.md §7.
         if (const char* e = std::getenv("PT_L2_WINDOW_MB")) {
@@ -648,6 +652,26 @@ int pt_readback(pt_ctx* c, float* rgba, size_t bytes) {
     CK(cudaMemcpyAsync(rgba, c->accum, need, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return collect_timing(c);
+}
+
+// calculateHdrCache (M:555-652) on a device, host buffers in and out: the stand-alone form of what pt_upload_scene does when
+// it is handed no table.
+int pt_calculate_hdr_cache(int device, const float* hdr, int width, int height, float* cache) {
+    if (!hdr || !cache || width <= 0 || height <= 0) return fail(PT_EINVAL, "pt_calculate_hdr_cache: null buffer or empty image");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(PT_EINVAL, "pt_calculate_hdr_cache: no such CUDA device");
+    CK(cudaSetDevice(device));
+    const size_t bytes = (size_t)width * height * 3 * sizeof(float);
+    float *d_rgb = nullptr, *d_out = nullptr;
+    cudaError_t e = cudaMalloc(&d_rgb, bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, bytes);
+    if (e == cudaSuccess) e = cudaMemcpy(d_rgb, hdr, bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = pt::hdr_cache_device(d_rgb, width, height, nullptr, d_out, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(cache, d_out, bytes, cudaMemcpyDeviceToHost);
+    cudaFree(d_rgb); cudaFree(d_out);
+    if (e != cudaSuccess) return fail(PT_ECUDA, std::string("pt_calculate_hdr_cache: ") + cudaGetErrorString(e));
+    return PT_OK;
 }
 
 int pt_readback_display(pt_ctx* c, unsigned char* rgba8, size_t bytes) {

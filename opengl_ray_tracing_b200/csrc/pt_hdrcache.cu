@@ -1,0 +1,129 @@
+// calculateHdrCache (ImportanceSampling_LowDiscrepancySequence/main.cpp:555-652, "M:") on the GPU — SURVEY.md §8f.3.
+//
+// The table is part of the spec bit for bit: its fp32 running sums drift (the pdf channel sums to 1.0001 … 1.0077 on the
+// shipped maps) and the shader inverts exactly that table.  So the sums that are sequential in the reference stay sequential
+// here, in the reference's order, with explicit round-to-nearest operations; what is independent runs in parallel:
+//   luminance (the one expression the reference evaluates in double, M:567)  one thread per texel
+//   lumSum over all texels, row-major (M:568)                                one thread, operands staged through shared memory
+//   pdf /= lumSum (M:573-576)                                                one thread per texel
+//   column marginals and conditional CDFs (M:579-609)                        one thread per column, rows in order
+//   cdf_x prefix over the columns (M:586-588)                                one thread
+//   the two lower_bound searches per table entry (M:621-636)                 one thread per entry, libstdc++'s halving loop
+// Checked bit for bit against libptscene's host restatement (itself checked against the reference's own code) in tests.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "pt_common.cuh"
+
+namespace pt {
+namespace {
+
+__global__ void k_luminance(const float* __restrict__ rgb, size_t n, float* __restrict__ pdf) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double r = (double)rgb[3 * i], g = (double)rgb[3 * i + 1], b = (double)rgb[3 * i + 2];
+    pdf[i] = __double2float_rn(__dadd_rn(__dadd_rn(__dmul_rn(0.2, r), __dmul_rn(0.7, g)), __dmul_rn(0.1, b)));
+}
+
+// lumSum += lum in texel order: the additions are one dependent chain, the loads are not
+#define PT_SEQ_CHUNK 4096
+__global__ void __launch_bounds__(1024) k_sequential_sum(const float* __restrict__ v, size_t n, float* __restrict__ out) {
+    __shared__ float stage[PT_SEQ_CHUNK];
+    float s = 0.0f;
+    for (size_t base = 0; base < n; base += PT_SEQ_CHUNK) {
+        for (int k = threadIdx.x; k < PT_SEQ_CHUNK; k += blockDim.x) stage[k] = base + k < n ? v[base + k] : 0.0f;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const int m = (int)(n - base < (size_t)PT_SEQ_CHUNK ? n - base : (size_t)PT_SEQ_CHUNK);
+            for (int k = 0; k < m; k++) s = __fadd_rn(s, stage[k]);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = s;
+}
+
+__global__ void k_normalise(float* __restrict__ pdf, size_t n, const float* __restrict__ lum_sum) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) pdf[i] = __fdiv_rn(pdf[i], *lum_sum);
+}
+
+// column j: pdf_x[j] = sum_i pdf[i][j]; cdf_y[j][i] = running sum of pdf[i][j] / pdf_x[j].  cdf_y is kept row-major
+// ([i][j]) so that both loops are coalesced across the columns.
+__global__ void k_columns(const float* __restrict__ pdf, int W, int H, float* __restrict__ pdf_x, float* __restrict__ cdf_y) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= W) return;
+    float s = 0.0f;
+    for (int i = 0; i < H; i++) s = __fadd_rn(s, pdf[(size_t)i * W + j]);
+    pdf_x[j] = s;
+    float run = 0.0f;
+    for (int i = 0; i < H; i++) {
+        const float cond = __fdiv_rn(pdf[(size_t)i * W + j], s);
+        run = i == 0 ? cond : __fadd_rn(run, cond);
+        cdf_y[(size_t)i * W + j] = run;
+    }
+}
+
+__global__ void k_prefix(const float* __restrict__ pdf_x, int W, float* __restrict__ cdf_x) {
+    if (blockIdx.x || threadIdx.x) return;
+    float run = pdf_x[0];
+    cdf_x[0] = run;
+    for (int j = 1; j < W; j++) { run = __fadd_rn(pdf_x[j], run); cdf_x[j] = run; }
+}
+
+// std::lower_bound as libstdc++ writes it (first position whose element is not < val), over a strided sequence
+__device__ __forceinline__ int lower_bound_strided(const float* __restrict__ a, size_t stride, int n, float val) {
+    int first = 0, len = n;
+    while (len > 0) {
+        const int half = len >> 1, middle = first + half;
+        if (a[(size_t)middle * stride] < val) { first = middle + 1; len = len - half - 1; }
+        else len = half;
+    }
+    return first;
+}
+
+// entry (i, j): xi_1 = i / H picks the column x through cdf_x, xi_2 = j / W the row y through column x's cdf (the
+// reference's transposed roles of i and j, M:621-636); out = (x / W, y / H, pdf[i][j])
+template <bool FLOAT4>
+__global__ void k_lookup(const float* __restrict__ pdf, const float* __restrict__ cdf_x, const float* __restrict__ cdf_y, int W, int H,
+                         float* __restrict__ out) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t)W * H) return;
+    const int i = (int)(idx / (size_t)W), j = (int)(idx - (size_t)i * W);
+    const float xi_1 = __fdiv_rn((float)i, (float)H), xi_2 = __fdiv_rn((float)j, (float)W);
+    int x = lower_bound_strided(cdf_x, 1, W, xi_1);
+    if (x >= W) x = W - 1;                             // the reference would index past the end here; never hit on real maps
+    const int y = lower_bound_strided(cdf_y + x, (size_t)W, H, xi_2);
+    const float ox = __fdiv_rn((float)x, (float)W), oy = __fdiv_rn((float)y, (float)H), op = pdf[idx];
+    if (FLOAT4) reinterpret_cast<float4*>(out)[idx] = make_float4(ox, oy, op, 0.0f);
+    else { out[3 * idx] = ox; out[3 * idx + 1] = oy; out[3 * idx + 2] = op; }
+}
+
+}  // namespace
+
+// d_rgb: W*H*3 floats on the device (file row order).  Exactly one of d_cache4 (W*H float4, the renderer's layout) and
+// d_cache3 (W*H*3 floats, the reference's layout) receives the table.  Temporaries are allocated and freed here.
+cudaError_t hdr_cache_device(const float* d_rgb, int W, int H, float4* d_cache4, float* d_cache3, cudaStream_t st) {
+    const size_t n = (size_t)W * H;
+    float *pdf = nullptr, *cdf_y = nullptr, *small = nullptr;
+    cudaError_t e = cudaMalloc(&pdf, n * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&cdf_y, n * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&small, (2 * (size_t)W + 1) * sizeof(float));
+    if (e == cudaSuccess) {
+        float *pdf_x = small, *cdf_x = small + W, *lum_sum = small + 2 * (size_t)W;
+        const unsigned blocks = (unsigned)((n + 255) / 256);
+        k_luminance<<<blocks, 256, 0, st>>>(d_rgb, n, pdf);
+        k_sequential_sum<<<1, 1024, 0, st>>>(pdf, n, lum_sum);
+        k_normalise<<<blocks, 256, 0, st>>>(pdf, n, lum_sum);
+        k_columns<<<(W + 127) / 128, 128, 0, st>>>(pdf, W, H, pdf_x, cdf_y);
+        k_prefix<<<1, 32, 0, st>>>(pdf_x, W, cdf_x);
+        if (d_cache4) k_lookup<true><<<blocks, 256, 0, st>>>(pdf, cdf_x, cdf_y, W, H, reinterpret_cast<float*>(d_cache4));
+        else k_lookup<false><<<blocks, 256, 0, st>>>(pdf, cdf_x, cdf_y, W, H, d_cache3);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    }
+    cudaFree(pdf); cudaFree(cdf_y); cudaFree(small);
+    return e;
+}
+
+}  // namespace pt

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -298,6 +299,77 @@ int pts_write_ppm_tonemapped(const char* path, const float* rgba, int w, int h) 
         std::fwrite(row.data(), 1, row.size(), f);
     }
     std::fclose(f);
+    return PTS_OK;
+}
+
+// 8-bit PNG for the display stage (the reference's CPU tracer writes its image through svpng, Basic/main.cpp:169-190,
+// a header that is absent from the tree).  Written from the PNG and zlib specifications: IHDR, ONE IDAT holding a zlib
+// stream of stored (uncompressed) deflate blocks, IEND; every scanline starts with filter byte 0.
+// `pixels` = height rows of width * channels bytes, top row first; channels 3 (RGB) or 4 (RGBA).
+namespace {
+struct PngOut {
+    FILE* f;
+    uint32_t crc;
+    static uint32_t table_entry(uint32_t n) {
+        for (int k = 0; k < 8; k++) n = (n & 1u) ? 0xedb88320u ^ (n >> 1) : n >> 1;
+        return n;
+    }
+    void raw(const unsigned char* p, size_t n) {
+        static uint32_t table[256];
+        static bool ready = false;
+        if (!ready) { for (uint32_t i = 0; i < 256; i++) table[i] = table_entry(i); ready = true; }
+        for (size_t i = 0; i < n; i++) crc = table[(crc ^ p[i]) & 0xffu] ^ (crc >> 8);
+        std::fwrite(p, 1, n, f);
+    }
+    void u8(unsigned v) { unsigned char b = (unsigned char)v; raw(&b, 1); }
+    void u16le(unsigned v) { u8(v & 0xffu); u8((v >> 8) & 0xffu); }
+    void u32be(uint32_t v) { u8(v >> 24); u8((v >> 16) & 0xffu); u8((v >> 8) & 0xffu); u8(v & 0xffu); }
+    void begin(const char* type, uint32_t length) { u32be(length); crc = 0xffffffffu; raw((const unsigned char*)type, 4); }
+    void end() { u32be(~crc); }
+};
+}  // namespace
+
+int pts_write_png(const char* path, const unsigned char* pixels, int w, int h, int channels) {
+    if (!path || !pixels || w <= 0 || h <= 0 || (channels != 3 && channels != 4)) return PTS_EINVAL;
+    FILE* f = std::fopen(path, "wb");
+    if (!f) { set_error(std::string("cannot write ") + path); return PTS_EIO; }
+    PngOut o{f, 0};
+    static const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    std::fwrite(sig, 1, 8, f);
+    o.begin("IHDR", 13);
+    o.u32be((uint32_t)w); o.u32be((uint32_t)h);
+    o.u8(8); o.u8(channels == 3 ? 2 : 6); o.u8(0); o.u8(0); o.u8(0);
+    o.end();
+    const size_t line = (size_t)w * channels + 1;                  // filter byte + pixels
+    const size_t total = line * (size_t)h;
+    const size_t nblocks = (total + 65534) / 65535;
+    o.begin("IDAT", (uint32_t)(2 + nblocks * 5 + total + 4));
+    o.u8(0x78); o.u8(0x01);                                        // zlib header: deflate, 32 K window, no preset dictionary
+    uint32_t a = 1, b = 0;                                         // Adler-32 of the uncompressed bytes
+    size_t in_block = 0, done = 0;
+    auto put = [&](unsigned char v) {
+        if (in_block == 0) {
+            const size_t n = std::min<size_t>(65535, total - done);
+            o.u8(done + n == total ? 1 : 0);                       // BFINAL, BTYPE = 00 (stored)
+            o.u16le((unsigned)n); o.u16le((unsigned)(~n & 0xffffu));
+            in_block = n;
+        }
+        o.u8(v);
+        a = (a + v) % 65521u; b = (b + a) % 65521u;
+        in_block--; done++;
+    };
+    for (int y = 0; y < h; y++) {
+        put(0);
+        const unsigned char* row = pixels + (size_t)y * w * channels;
+        for (size_t i = 0; i < (size_t)w * channels; i++) put(row[i]);
+    }
+    o.u32be((b << 16) | a);
+    o.end();
+    o.begin("IEND", 0);
+    o.end();
+    const bool ok = !std::ferror(f);
+    std::fclose(f);
+    if (!ok) { set_error(std::string("write error on ") + path); return PTS_EIO; }
     return PTS_OK;
 }
 

@@ -24,7 +24,7 @@ ACC_MEAN, ACC_SUM = 0, 1
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
-           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_last_error",
+           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_last_error",
            "pt_build_info"]
 
 
@@ -79,6 +79,7 @@ def lib():
         "pt_get_ray_histogram": (C.c_int, [vp, C.POINTER(C.c_ulonglong), C.c_int]),
         "pt_last_error": (C.c_char_p, []),
         "pt_build_info": (C.c_char_p, []),
+        "pt_calculate_hdr_cache": (C.c_int, [C.c_int, C.POINTER(C.c_float), C.c_int, C.c_int, C.POINTER(C.c_float)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -217,3 +218,14 @@ class PathTracer:
 
 def build_info() -> str:
     return lib().pt_build_info().decode()
+
+
+def calculate_hdr_cache(hdr, device=0):
+    """calculateHdrCache (M:555-652) on the GPU: hdr float32 [H, W, 3] -> table float32 [H, W, 3], bit for bit the host table."""
+    h = np.ascontiguousarray(hdr, dtype=np.float32)
+    if h.ndim != 3 or h.shape[2] != 3:
+        raise ValueError("calculate_hdr_cache: need float32 [H, W, 3]")
+    out = np.empty_like(h)
+    f32p = C.POINTER(C.c_float)
+    _check(lib().pt_calculate_hdr_cache(device, h.ctypes.data_as(f32p), h.shape[1], h.shape[0], out.ctypes.data_as(f32p)), "pt_calculate_hdr_cache")
+    return out

@@ -67,6 +67,7 @@ def lib():
         "pts_free": (None, [vp]),
         "pts_write_pfm": (C.c_int, [C.c_char_p, f32p, C.c_int, C.c_int]),
         "pts_write_ppm_tonemapped": (C.c_int, [C.c_char_p, f32p, C.c_int, C.c_int]),
+        "pts_write_png": (C.c_int, [C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
         "pts_last_error": (C.c_char_p, []),
     }
     for name, (res, args) in sig.items():
@@ -81,7 +82,7 @@ EXPORTS = ["pts_material_default", "pts_get_transform_matrix", "pts_camera", "pt
            "pts_add_quad", "pts_write_obj_icosphere", "pts_triangle_count", "pts_node_count",
            "pts_build_bvh", "pts_triangles_encoded", "pts_nodes_encoded", "pts_scene_save",
            "pts_scene_load", "pts_hdr_load", "pts_hdr_write", "pts_hdr_cache", "pts_hdr_synth", "pts_free",
-           "pts_write_pfm", "pts_write_ppm_tonemapped", "pts_last_error"]
+           "pts_write_pfm", "pts_write_ppm_tonemapped", "pts_write_png", "pts_last_error"]
 
 
 class SceneError(RuntimeError):
@@ -263,6 +264,14 @@ def writeHdr(path, data):
 def writePfm(path, rgba):
     d = _f32(rgba)
     _check(lib().pts_write_pfm(os.fsencode(path), _fp(d), d.shape[1], d.shape[0]), "writePfm")
+
+
+def writePng(path, pixels):
+    """pixels: uint8 [H, W, 3 or 4], top row first (what PathTracer.readback_display returns)."""
+    d = np.ascontiguousarray(pixels, dtype=np.uint8)
+    if d.ndim != 3 or d.shape[2] not in (3, 4):
+        raise ValueError("writePng: need uint8 [H, W, 3|4]")
+    _check(lib().pts_write_png(os.fsencode(path), d.ctypes.data, d.shape[1], d.shape[0], d.shape[2]), "writePng")
 
 
 def writePpmTonemapped(path, rgba):

@@ -192,8 +192,7 @@ def test_error_behaviour(R):
     with pytest.raises(R.PtError, match="no scene"):
         pt.render_spp(0, 1)
     sc = small_scene("is", "1k")
-    with pytest.raises(R.PtError, match="hdrCache"):
-        pt.upload_scene(sc.tris, sc.nodes, sc.hdr, None)
+    assert L.pt_calculate_hdr_cache(0, None, 4, 4, None) < 0 and b"null buffer" in L.pt_last_error()
     bad = sc.nodes.copy(); bad[1, 0] = 1.0                    # root's left child = itself
     with pytest.raises(R.PtError, match="child index"):
         pt.upload_scene(sc.tris, bad, sc.hdr, sc.hdrCache)
@@ -337,3 +336,31 @@ def test_display_pass_matches_pass3(R):
     assert disp.shape == (H, W, 4) and (disp[..., 3] == 255).all()
     assert (disp[..., :3] == want).all()
     assert disp[..., :3].std() > 0
+
+
+@pytest.mark.gpu
+def test_hdr_cache_on_the_gpu_is_the_host_table_bit_for_bit(R):
+    """calculateHdrCache (M:555-652) on the device vs libptscene's host restatement (itself pinned to the reference's code)."""
+    from opengl_ray_tracing_b200 import scene as S
+    rng = np.random.default_rng(5)
+    maps = [S.synthHdr(512, 256, 1), S.synthHdr(2048, 1024, 3), S.synthHdr(96, 40, 2),
+            (rng.random((33, 70, 3), dtype=np.float32) ** 8 * 50).astype(np.float32),           # ragged size, spiky
+            np.ones((8, 8, 3), np.float32)]                                                     # flat: long runs of equal cdf steps
+    for hdr in maps:
+        want = S.calculateHdrCache(hdr, hdr.shape[1], hdr.shape[0])
+        got = R.calculate_hdr_cache(hdr)
+        assert got.shape == want.shape and got.tobytes() == np.ascontiguousarray(want, np.float32).tobytes()
+
+
+@pytest.mark.gpu
+def test_upload_without_a_table_builds_it_on_the_device(R):
+    sc = small_scene("is", "1k")
+    W, H, NF = 96, 64, 3
+    a, ids_a, _, _ = render(R, sc, W, H, 0, NF, R.MODE_PARITY_FAST)
+    pt = R.PathTracer(W, H, sc.variant, mode=R.MODE_PARITY_FAST)
+    pt.upload_scene(sc.tris, sc.nodes, sc.hdr, None)           # variant 2 with hdrCache = NULL
+    pt.set_camera(sc.eye, sc.cam)
+    pt.render_spp(0, NF)
+    b = pt.readback()
+    pt.close()
+    assert a.tobytes() == b.tobytes()
