@@ -415,6 +415,15 @@ def run_ours(args):
             basic = basic_tracer_baseline()
             if basic is not None:
                 line["cpu_baseline_basic"] = basic
+            # BASELINE.json config 1 on the GPU: the same tracer (pt_basic_render), same 256x256 x 200 samples
+            from opengl_ray_tracing_b200 import basic as PB
+            shapes = PB.default_scene()
+            PB.render(shapes, 256, 256, 8)                                     # warm-up
+            t0 = time.perf_counter()
+            _, ms = PB.render(shapes, 256, 256, 200)
+            wall = time.perf_counter() - t0
+            line["basic_gpu"] = {"value": 256 * 256 * 200 / wall / 1e6, "unit": "Mpaths/s", "seconds": wall, "device_ms": ms,
+                                 "sample": "pt_basic_render, 256x256 Cornell box, 200 samples, wall clock incl. the image copy back"}
         print(json.dumps(line), flush=True)
     pt.close()
     if world > 1:

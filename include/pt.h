@@ -173,6 +173,29 @@ int pt_reset_stats(pt_ctx* ctx);
    bucket k counts rays with 2^(k-1) <= steps < 2^k (bucket 0: no step).  n >= 33. */
 int pt_get_ray_histogram(pt_ctx* ctx, unsigned long long* buckets, int n);
 
+/* ---- BasicRayTracingWithC++/main.cpp ("B:") on the GPU: SURVEY.md 8f.4, BASELINE.json config 1 ----------------------
+   The reference's CPU tracer has no entry point but main(); these three calls are its scene literal (B:304-353), its
+   sample loop (B:355-432) and its imshow conversion (B:169-190).  Same arithmetic operation for operation; the random
+   numbers come from a counter-based stream keyed by (seed, sample, row, column) instead of the reference's shared,
+   random_device-seeded mt19937, so runs are reproducible (oracle: the reference's own source with that stream). */
+typedef struct PtBasicShape {        /* class Triangle / class Sphere + struct Material, B:48-58, B:77-166 */
+    int kind;                        /* 0 = Triangle(p1, p2, p3), 1 = Sphere(O = p1, R = radius) */
+    float p1[3], p2[3], p3[3];
+    double radius;
+    float color[3];
+    int isEmissive;
+    double specularRate, roughness, refractRate, refractAngle, refractRoughness;
+} PtBasicShape;
+/* Writes up to `capacity` shapes of the reference's Cornell box; returns how many it has (17). */
+int pt_basic_default_scene(PtBasicShape* shapes, int capacity);
+/* image: height*width*3 doubles, row 0 = top: the per-pixel SUM over `samples` passes (what imshow receives).
+   device_ms (optional): device time of the kernels.  At most 64 shapes (brute-force closest hit, like shoot(), B:192-205). */
+int pt_basic_render(int device, const PtBasicShape* shapes, int n_shapes, int width, int height, int samples, unsigned seed,
+                    double* image, double* device_ms);
+/* imshow without the file: gamma 1/2.2, x255, clamp, truncate -> height*width*3 bytes (feed to pts_write_png). */
+int pt_basic_imshow(const double* image, int width, int height, unsigned char* rgb8);
+const char* pt_basic_last_error(void);
+
 const char* pt_last_error(void);
 /* "sm_100a" build tag + whether a CUDA device is visible; never fails (used by the CPU-only symbol test) */
 const char* pt_build_info(void);

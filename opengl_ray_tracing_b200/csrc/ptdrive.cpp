@@ -32,6 +32,9 @@ struct Options {
     unsigned spp = 64, per_call = 64;
     float up = 0.0f, rot = 0.0f, r = 4.0f;   // M:147-149
     int sah = 1, threads = 0, mode = PT_MODE_FAST, pipeline = PT_PIPELINE_PERSISTENT, device = 0, max_bounce = 0;
+    bool basic = false;                 // --basic: BasicRayTracingWithC++/main.cpp instead (its own scene literal, 256x256)
+    unsigned seed = 1;
+    bool size_given = false;
 };
 
 [[noreturn]] void die(const std::string& msg) {
@@ -42,7 +45,8 @@ struct Options {
 void usage() {
     std::puts("ptdrive [--variant 0|1|2] [--obj FILE | --icosphere N] [--hdr FILE | --synth-hdr WxH] [--size WxH] [--spp N]\n"
               "        [--spp-per-call K] [--camera UP,ROT,R] [--median] [--threads T] [--mode M] [--pipeline P] [--device D]\n"
-              "        [--max-bounce B] [--out image.png] [--pfm radiance.pfm]");
+              "        [--max-bounce B] [--out image.png] [--pfm radiance.pfm]\n"
+              "ptdrive --basic [--size WxH] [--spp N] [--seed S] [--device D] [--out image.png]      (BasicRayTracingWithC++/main.cpp)");
 }
 
 bool parse_pair(const char* s, char sep, int& a, int& b) {
@@ -62,7 +66,9 @@ Options parse(int argc, char** argv) {
         else if (a == "--icosphere") o.icosphere = std::atoi(next());
         else if (a == "--hdr") o.hdr = next();
         else if (a == "--synth-hdr") { if (!parse_pair(next(), 'x', o.hdr_w, o.hdr_h)) die("--synth-hdr wants WxH"); }
-        else if (a == "--size") { if (!parse_pair(next(), 'x', o.width, o.height)) die("--size wants WxH"); }
+        else if (a == "--size") { if (!parse_pair(next(), 'x', o.width, o.height)) die("--size wants WxH"); o.size_given = true; }
+        else if (a == "--basic") o.basic = true;
+        else if (a == "--seed") o.seed = (unsigned)std::strtoul(next(), nullptr, 10);
         else if (a == "--spp") o.spp = (unsigned)std::atoi(next());
         else if (a == "--spp-per-call") o.per_call = (unsigned)std::atoi(next());
         else if (a == "--camera") { if (std::sscanf(next(), "%f,%f,%f", &o.up, &o.rot, &o.r) != 3) die("--camera wants UP,ROT,R"); }
@@ -134,11 +140,30 @@ void populate(pts_scene* sc, const Options& o) {
     }
 }
 
+// BasicRayTracingWithC++/main.cpp: scene literal, SAMPLE passes, imshow -> PNG (B:300-441)
+int run_basic(const Options& o) {
+    const int w = o.size_given ? o.width : 256, h = o.size_given ? o.height : 256;      // B:23-24
+    PtBasicShape shapes[64];
+    const int n = pt_basic_default_scene(shapes, 64);
+    std::vector<double> image((size_t)w * h * 3);
+    double ms = 0.0;
+    const double t0 = now();
+    if (pt_basic_render(o.device, shapes, n, w, h, (int)o.spp, o.seed, image.data(), &ms) != PT_OK) die(std::string("pt_basic_render: ") + pt_basic_last_error());
+    std::printf("finish in %.3f seconds (%.2f ms on the device), %d shapes, %dx%d, %u samples, %.1f Mpaths/s\n", now() - t0, ms, n, w, h, o.spp,
+                (double)w * h * o.spp / (ms * 1e3));
+    std::vector<unsigned char> rgb((size_t)w * h * 3);
+    if (pt_basic_imshow(image.data(), w, h, rgb.data()) != PT_OK) die(pt_basic_last_error());
+    ptscheck(pts_write_png(o.out.c_str(), rgb.data(), w, h, 3), "pts_write_png");
+    std::printf("wrote %s\n", o.out.c_str());
+    return 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
     const Options o = parse(argc, argv);
     std::printf("%s\n", pt_build_info());
+    if (o.basic) return run_basic(o);
 
     // ---- scene, BVH, encoded arrays (M:752-821) ----
     double t0 = now();

@@ -11,6 +11,7 @@ Outputs:
                                  C++ (see glsl_compat.h / ref_shader_wrap.cpp); math in {libm, ptmath}
   basic_tracer                   BasicRayTracingWithC++/main.cpp, g++ -O3 -fopenmp, SAMPLE overridable
                                  through the REF_SAMPLE macro (the only edit: `const int SAMPLE = 128`)
+  libref_basic_det.so            the same source with a reproducible random stream, as a library (ref_basic_wrap.cpp)
 """
 import os
 import re
@@ -154,6 +155,45 @@ def build_basic():
     run(["cp", exe + "_200spp", exe])
 
 
+def build_basic_det():
+    """libref_basic_det.so: the same source with a reproducible random stream (oracle/ref_basic_wrap.cpp says what is edited)."""
+    src = os.path.join(REF, "BasicRayTracingWithC++", "main.cpp")
+    wrap = os.path.join(HERE, "ref_basic_wrap.cpp")
+    so = os.path.join(OUT, "libref_basic_det.so")
+    if newer(so, src, wrap, __file__):
+        return
+    with open(src, "r", encoding="latin-1") as f:
+        t = f.read().replace("\r\n", "\n")
+
+    def sub1(old, new, start=0):
+        nonlocal t
+        i = t.find(old, start)
+        assert i >= 0 and t.find(old, i + 1) < 0 or start > 0, old
+        t = t[:i] + new + t[i + len(old):]
+
+    sub1("const int SAMPLE = 128;", "static int SAMPLE = 128;")
+    sub1("const double BRIGHTNESS = (2.0f * 3.1415926f) * (1.0f / double(SAMPLE));",
+         "#define BRIGHTNESS ((2.0f * 3.1415926f) * (1.0f / double(SAMPLE)))")
+    sub1("const int WIDTH = 256;", "static int WIDTH = 256;")
+    sub1("const int HEIGHT = 256;", "static int HEIGHT = 256;")
+    sub1("return dis(gen);", "return det_randf();")
+    sub1('#include "svpng.inc"', "static void svpng(FILE*, unsigned, unsigned, const unsigned char*, int) {}")
+    m = t.find("int main()")
+    assert m >= 0
+    sub1("int main()", "static int ref_basic_main()")
+    sub1("omp_set_num_threads(50);", "omp_set_num_threads(1);")
+    loop = "for (int j = 0; j < WIDTH; j++)\n            {"
+    j = t.find(loop, m)
+    assert j >= 0
+    t = t[:j + len(loop)] + "\n                det_seed(k, i, j);" + t[j + len(loop):]
+    sub1('imshow(image, "basic_ray_tracing_with_c++.png");', "det_export(image);")
+    with open(os.path.join(OUT, "basic_det.inc"), "w", encoding="latin-1") as f:
+        f.write(t)
+    run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-w", "-shared",
+         "-include", "cstring", "-include", "cstdio", "-Dfopen_s(pf,n,m)=((*(pf)=fopen(n,m))==0)",
+         "-I", OUT, "-I", os.path.join(REF, "include"), wrap, "-o", so])
+
+
 def main():
     if not os.path.isdir(REF):
         print("build_ref: %s not present (GPU box?) — using prebuilt oracle/_ref as is" % REF)
@@ -163,6 +203,7 @@ def main():
     build_shaders()
     if "--no-basic" not in sys.argv:
         build_basic()
+        build_basic_det()
     return 0
 
 

@@ -22,7 +22,12 @@ def test_libpt_exports_every_declared_symbol():
     L = C.CDLL(os.path.join(ROOT, "opengl_ray_tracing_b200", "libpt.so"))
     for n in names:
         assert hasattr(L, n), "libpt.so lacks " + n
-    assert sorted(R.EXPORTS) == names, "renderer.py's binding list is out of sync with include/pt.h"
+    from opengl_ray_tracing_b200 import basic as B
+    basic = sorted(n for n in names if n.startswith("pt_basic_"))          # bound by basic.py
+    assert basic == ["pt_basic_default_scene", "pt_basic_imshow", "pt_basic_last_error", "pt_basic_render"]
+    B._lib()
+    assert sorted(R.EXPORTS + basic) == names, "renderer.py / basic.py binding lists are out of sync with include/pt.h"
+    assert C.sizeof(B.PtBasicShape) == 104
 
 
 def test_libptscene_exports_every_declared_symbol():

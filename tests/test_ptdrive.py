@@ -95,3 +95,13 @@ def test_ptdrive_image_equals_the_python_mirror(tmp_path, variant, kind):
         assert f.readline() == b"PF\n" and f.readline() == b"%d %d\n" % (W, H) and f.readline() == b"-1.0\n"
         rad = np.frombuffer(f.read(), "<f4").reshape(H, W, 3)
     assert rad.tobytes() == np.ascontiguousarray(want[..., :3]).tobytes()
+
+
+@pytest.mark.gpu
+def test_ptdrive_basic_writes_the_reference_tracers_image(tmp_path):
+    from opengl_ray_tracing_b200 import basic as B
+    png = str(tmp_path / "basic.png")
+    r = subprocess.run([PTDRIVE, "--basic", "--size", "64x48", "--spp", "5", "--seed", "9", "--out", png], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    img, _ = B.render(B.default_scene(), 64, 48, 5, 9)
+    assert (decode_png(png) == B.imshow(img)).all()
