@@ -71,12 +71,26 @@ __device__ __forceinline__ bool hit_triangle(const Ray& r, V3 p1, V3 p2, V3 p3, 
 }
 
 // The culling form of the slab test, for the padded boxes of the production tree: same products and the same
-// NaN-dropping min/max nesting as hit_aabb, but only the decision "hitAABB(...) > 0 and entry <= cull" is formed:
+// Culling test of the production traversal: the decision "hitAABB(...) > 0 and entry <= cull",
 //   hitAABB > 0  <=>  t1 >= t0 and t1 > 0   (t0 > 0 implies t1 > 0; otherwise the returned value is t1)
-__device__ __forceinline__ bool slab_cull(const Ray& r, V3 AA, V3 BB, float cull, float& entry) {
-    float fx = s_mul(s_sub(BB.x, r.o.x), r.inv.x), nx = s_mul(s_sub(AA.x, r.o.x), r.inv.x);
-    float fy = s_mul(s_sub(BB.y, r.o.y), r.inv.y), ny = s_mul(s_sub(AA.y, r.o.y), r.inv.y);
-    float fz = s_mul(s_sub(BB.z, r.o.z), r.inv.z), nz = s_mul(s_sub(AA.z, r.o.z), r.inv.z);
+// with hit_aabb's NaN-dropping min/max nesting.
+// The PRODUCTION tree's boxes only cull (padded by 2^-17 of the scene radius, pt_build.cpp): one
+// fused multiply-add per plane, t = box * (1/d) - o * (1/d), instead of a subtraction and a multiplication.  The fused
+// form is off by a few ulps of the ORIGIN's coordinates (6e-8 |o| in space), some fifty times less than the padding, so
+// "passes" stays a superset of "hitTriangle accepts"; what the reference's own boxes decide is tested exactly, per
+// candidate, with hit_aabb.  1/d is clamped to +-1e18 here: with an infinite 1/d the fused form gives inf - inf = NaN on
+// BOTH planes of a slab the origin lies in, and the NaN-dropping min/max would then reject a ray that passes.
+struct CullRay { V3 inv, noi; };                      // clamped 1/d and -(o * that)
+__device__ __forceinline__ CullRay make_cull_ray(const Ray& r) {
+    CullRay c;
+    c.inv = mk3(fminf(fmaxf(r.inv.x, -1e18f), 1e18f), fminf(fmaxf(r.inv.y, -1e18f), 1e18f), fminf(fmaxf(r.inv.z, -1e18f), 1e18f));
+    c.noi = mk3(-s_mul(r.o.x, c.inv.x), -s_mul(r.o.y, c.inv.y), -s_mul(r.o.z, c.inv.z));
+    return c;
+}
+__device__ __forceinline__ bool slab_cull_fused(const CullRay& c, V3 AA, V3 BB, float cull, float& entry) {
+    float fx = __fmaf_rn(BB.x, c.inv.x, c.noi.x), nx = __fmaf_rn(AA.x, c.inv.x, c.noi.x);
+    float fy = __fmaf_rn(BB.y, c.inv.y, c.noi.y), ny = __fmaf_rn(AA.y, c.inv.y, c.noi.y);
+    float fz = __fmaf_rn(BB.z, c.inv.z, c.noi.z), nz = __fmaf_rn(AA.z, c.inv.z, c.noi.z);
     float t1 = fminf(fmaxf(fx, nx), fminf(fmaxf(fy, ny), fmaxf(fz, nz)));
     float t0 = fmaxf(fminf(fx, nx), fmaxf(fminf(fy, ny), fminf(fz, nz)));
     entry = fmaxf(t0, 0.0f);
@@ -269,6 +283,7 @@ template <> struct Counter<false> {
 template <int STACK, class CNT>
 __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin, V3 dir, const bool anyhit, CNT& cnt) {
     Ray r = make_ray(origin, dir);
+    const CullRay cr = make_cull_ray(r);
     TraceResult res; res.tri = -1; res.t = PT_INF; res.inside = false;
     float cull = PT_INF;
     bool tie = false;
@@ -282,8 +297,8 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
             const float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
             cnt.inner();
             float e1, e2;
-            const bool g1 = slab_cull(r, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), cull, e1);
-            const bool g2 = slab_cull(r, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), cull, e2);
+            const bool g1 = slab_cull_fused(cr, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), cull, e1);
+            const bool g2 = slab_cull_fused(cr, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), cull, e2);
             const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
             if (g1 && g2) {
                 const bool left_first = e1 <= e2;
