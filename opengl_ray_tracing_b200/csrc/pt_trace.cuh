@@ -70,7 +70,6 @@ __device__ __forceinline__ bool hit_triangle(const Ray& r, V3 p1, V3 p2, V3 p3, 
     return true;
 }
 
-// The culling form of the slab test, for the padded boxes of the production tree: same products and the same
 // Culling test of the production traversal: the decision "hitAABB(...) > 0 and entry <= cull",
 //   hitAABB > 0  <=>  t1 >= t0 and t1 > 0   (t0 > 0 implies t1 > 0; otherwise the returned value is t1)
 // with hit_aabb's NaN-dropping min/max nesting.
