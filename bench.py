@@ -38,6 +38,8 @@ WORKLOADS = {
     "disney-1M-1080p": ("disney", "1M", 1920, 1080, (1024, 512)),   # config 3
     "lambert-100k-1080p": ("lambert", "100k", 1920, 1080, (1024, 512)),  # config 2
     "full-10M-4k": ("full", "10M", 3840, 2160, (2048, 1024)),       # config 5 (reference tree from buildBVH, see build_workload)
+    "is-1M-4k": ("is", "1M", 3840, 2160, (2048, 1024)),             # the metric scene at 4K (scheduler tuning)
+    "is-1M-480p": ("is", "1M", 854, 480, (2048, 1024)),
     "is-100k-1080p": ("is", "100k", 1920, 1080, (2048, 1024)),      # quick variant for development
     "is-10k-480p": ("is", "10k", 854, 480, (512, 256)),
 }

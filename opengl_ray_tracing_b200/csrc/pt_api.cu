@@ -586,6 +586,11 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
         CK(cudaMalloc(&c->sched, (64 + ntiles) * sizeof(uint32_t)));
     }
     p.sched = c->sched;
+    {
+        // visiting order of the tile rows (render_persistent): 0 = the kernel's own rule, PT_SCHED_STRIDE=1 = bottom to top
+        const char* e = std::getenv("PT_SCHED_STRIDE");
+        p.sched_stride = e && *e ? (uint32_t)std::max(0, std::atoi(e)) : 0u;
+    }
     p.sobol_tab = nullptr;
     if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS && !wavefront) {
         if (c->sobol_cap < n_frames) {

@@ -569,6 +569,15 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
     const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
     const uint32_t ntiles = tm.count();                // owned 8x4 warp tiles
     const uint32_t nitems = ntiles * p.n_frames;
+    // Order of the tile rows inside a frame: S passes over the rows a, a + S, a + 2S, ... (a = 0 .. S-1) instead of bottom to
+    // top.  On the metric scene the lower half of the image is floor (three rays and two BRDF evaluations per sample: issue
+    // bound) and the upper half sky (one trivial ray: bound by the framebuffer stream); bottom to top, the resident warps
+    // are all of one kind at any time.  With one pass ~ 1.35 x the resident warps the two kinds overlap: +5.8 % at 1080p
+    // (S = 8), +6.5 % at 4K (S = 32), the measured optimum at both; scenes without such a split (variants 0 and 1 here) are
+    // neutral to -2.5 %, so the rule is applied to variant 2 only.  PT_SCHED_STRIDE overrides.  DESIGN.md §5.
+    uint32_t S = p.sched_stride;
+    if (S == 0u) S = VARIANT == 2 ? max(1u, (uint32_t)(0.74f * (float)ntiles / (float)(gridDim.x * 8u) + 0.5f)) : 1u;
+    S = min(S, max(1u, (uint32_t)tm.rows));
     uint32_t* head = p.sched;                          // [0] = next item; progress starts 64 words in
     uint32_t* progress = p.sched + 64;
     uint32_t nrays = 0;
@@ -582,7 +591,13 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
         // frame = item - ntiles) always lies in an EARLIER chunk, so waits point strictly backwards: no deadlock
 #pragma unroll 1
         for (uint32_t item = first_item; item < first_item + PT_PERSIST_CHUNK && item < nitems; item++) {
-            const uint32_t f = item / ntiles, tile = item - f * ntiles;
+            const uint32_t f = item / ntiles, t0 = item - f * ntiles;
+            const uint32_t row0 = t0 / (uint32_t)tm.per_row, j0 = t0 - row0 * (uint32_t)tm.per_row;
+            const uint32_t R = (uint32_t)tm.rows, q = R / S, rem = R - q * S;
+            uint32_t a, k;
+            if (row0 < rem * (q + 1)) { a = row0 / (q + 1); k = row0 - a * (q + 1); }
+            else { const uint32_t i2 = row0 - rem * (q + 1); a = rem + i2 / q; k = i2 - (a - rem) * q; }
+            const uint32_t tile = (a + k * S) * (uint32_t)tm.per_row + j0;
             int tx, strip;
             tm.locate(tile, tx, strip);
             const int px = p.x0 + tx * 8 + (lane & 7);
