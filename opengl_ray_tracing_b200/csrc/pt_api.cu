@@ -33,6 +33,8 @@ struct FastTree {
 void build_fast_tree(const float* tris_raw, int nTriangles, const float* nodes_raw, int nNodes, FastTree& out, int threads);
 cudaError_t hdr_cache_device(const float* d_rgb, int W, int H, float4* d_cache4, float* d_cache3, cudaStream_t st);   // pt_hdrcache.cu
 cudaError_t launch_fast(const RenderParams& p, int variant, bool count, cudaStream_t stream);
+cudaError_t build_light_table_parity(const DevScene& sc, float4* tab, cudaStream_t stream);   // pt_kernels_parity.cu
+cudaError_t build_light_table_fast(const DevScene& sc, float4* tab, cudaStream_t stream);     // pt_kernels_fast.cu
 cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
 cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
 cudaError_t launch_persistent_parity(const RenderParams& p, int variant, int which, int grid, cudaStream_t stream);
@@ -70,7 +72,7 @@ struct pt_ctx {
     int fast_depth = 0, n_fast_inner = 0;
     double build_ms = 0.0;
     float *tris_raw = nullptr, *nodes_raw = nullptr;
-    float4 *wnodes = nullptr, *wnodes_fast = nullptr, *trigeo_fast = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr;
+    float4 *wnodes = nullptr, *wnodes_fast = nullptr, *trigeo_fast = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr, *light_tab = nullptr;
     int2* trimeta = nullptr;
     pt::DevScene sc;
     // camera + region
@@ -194,9 +196,9 @@ void free_scene(pt_ctx* c) {
     cudaFree(c->trigeo_fast); cudaFree(c->trimeta);
     c->trigeo_fast = nullptr; c->trimeta = nullptr;
     cudaFree(c->tris_raw); cudaFree(c->nodes_raw); cudaFree(c->wnodes); cudaFree(c->wnodes_fast); cudaFree(c->trigeo); cudaFree(c->trishade);
-    cudaFree(c->materials); cudaFree(c->hdr4); cudaFree(c->cache4);
+    cudaFree(c->materials); cudaFree(c->hdr4); cudaFree(c->cache4); cudaFree(c->light_tab);
     c->tris_raw = c->nodes_raw = nullptr;
-    c->wnodes = c->wnodes_fast = c->trigeo = c->trishade = c->materials = c->hdr4 = c->cache4 = nullptr;
+    c->wnodes = c->wnodes_fast = c->trigeo = c->trishade = c->materials = c->hdr4 = c->cache4 = c->light_tab = nullptr;
     c->has_scene = false;
 }
 
@@ -468,6 +470,16 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         // root = node 1: a leaf when the whole scene fits one leaf, else wide node 0
         int rn = (int)nodes[12 + 3], rindex = (int)nodes[12 + 4];
         s.root_ref = rn > 0 ? pt::ref_pack((uint32_t)rindex, (uint32_t)rn) : pt::ref_pack(0u, 0u);
+        s.light_tab = nullptr;
+        if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS && c->cache4 && c->cfg.mode != PT_MODE_PARITY_REF) {
+            // light table: what a light sample through each hdrCache texel evaluates to, in this context's arithmetic (pt_shade.cuh)
+            CKU(cudaMalloc(&c->light_tab, ntex * 2 * sizeof(float4)));
+            const bool fast = c->cfg.mode == PT_MODE_FAST || c->cfg.mode == PT_MODE_FAST_COUNT;
+            CKU(fast ? pt::build_light_table_fast(s, c->light_tab, st) : pt::build_light_table_parity(s, c->light_tab, st));
+            CKU(cudaStreamSynchronize(st));
+            s.light_tab = c->light_tab;
+            c->launches += 1;
+        }
         c->has_scene = true;
         c->launches += 5 + (hdrCache ? 1 : cache_launches);
         // Optional L2 persistence window over the production tree's nodes (north star item 2); PT_L2_WINDOW_MB=0 (default)

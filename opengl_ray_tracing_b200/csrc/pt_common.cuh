@@ -83,6 +83,7 @@ struct DevScene {
     const float4* materials;    // nMaterials x 4 float4 (64 B)
     const float4* hdr4;         // hdrH x hdrW float4 (rgb, 0)
     const float4* cache4;       // hdrH x hdrW float4 (x/w, y/h, pdf, 0) or null
+    const float4* light_tab;    // hdrH x hdrW x 2 float4: what a light sample through each cache texel evaluates to (pt_shade.cuh) or null
     int nTriangles, nNodes, nInner, nMaterials;
     int hdrW, hdrH;
     uint32_t root_ref, root_fast;

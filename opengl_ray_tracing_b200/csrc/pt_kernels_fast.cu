@@ -16,4 +16,5 @@ cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count
     if (count) return launch_wavefront<CfgFastCount>(p, variant, grid, stream);
     return launch_wavefront<CfgFast>(p, variant, grid, stream);
 }
+cudaError_t build_light_table_fast(const DevScene& sc, float4* tab, cudaStream_t stream) { return build_light_table<CfgFast>(sc, tab, stream); }
 }  // namespace pt

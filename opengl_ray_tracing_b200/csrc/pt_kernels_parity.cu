@@ -21,4 +21,5 @@ cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int whic
     if (which == 2) return launch_wavefront<CfgParityWide>(p, variant, grid, stream);
     return launch_wavefront<CfgParityFast>(p, variant, grid, stream);
 }
+cudaError_t build_light_table_parity(const DevScene& sc, float4* tab, cudaStream_t stream) { return build_light_table<CfgParityWide>(sc, tab, stream); }
 }  // namespace pt

@@ -42,11 +42,11 @@ struct MathFast {                 // SFU approximations where CUDA has them
     static __device__ __forceinline__ float log(float a) { return __logf(a); }
     static __device__ __forceinline__ float pow(float a, float b) { return __powf(a, b); }
 };
-struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; static const bool COUNT = false; };
-struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; };
-struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; };
-struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; };
-struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  };
+struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = false; };
+struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = true; };
+struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true; };
+struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true; };
+struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  static const bool LIGHT_TAB = true; };
 
 // counting configuration: histogram of traversal steps (inner nodes + triangles) per ray, log2 buckets
 __device__ __forceinline__ uint32_t ray_steps(const Counter<false>&) { return 0; }
@@ -175,13 +175,42 @@ template <class M> __device__ __forceinline__ float hdr_pdf(const DevScene& sc, 
     float p_convert = (float)(sc.hdrW * sc.hdrW / 2) / (2.0f * PT_PI * PT_PI * sin_theta);
     return pdf * p_convert;
 }
-template <class M> __device__ __forceinline__ V3 SampleHdr(const DevScene& sc, float xi_1, float xi_2) {   // P:573-585
-    float4 c = tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, xi_1, xi_2);
+__device__ __forceinline__ V3 hdr_entry_direction(float4 c) {                                              // P:575-584
     float x = c.x, y = s_sub(1.0f, c.y);
     float phi = s_mul(s_mul(2.0f, PT_PI), s_sub(x, 0.5f));
     float theta = s_mul(PT_PI, s_sub(y, 0.5f));
     float ct = pt_cosf(theta);
     return mk3(s_mul(ct, pt_cosf(phi)), pt_sinf(theta), s_mul(ct, pt_sinf(phi)));
+}
+template <class M> __device__ __forceinline__ V3 SampleHdr(const DevScene& sc, float xi_1, float xi_2) {   // P:573-585
+    return hdr_entry_direction(tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, xi_1, xi_2));
+}
+
+// ---- light table (Cfg::LIGHT_TAB) ------------------------------------------------------------------------
+// Everything the light-sampling half of a bounce computes from its two random numbers is a function of the hdrCache TEXEL
+// they select (P:573-585: NEAREST lookup, then a direction from the entry): the direction Ld (two sines, two cosines), and,
+// if the shadow ray escapes, hdrColor(Ld) and hdrPdf(Ld) (P:647-666: normalize, atan, asin, two more texel fetches, a sine,
+// a division).  There are only W x H such texels, so the upload evaluates those very functions once per texel, with the
+// arithmetic of the mode the context renders in, and the render kernel reads the results back: bit for bit what the
+// straight-line code computes, ~350 instructions and two scattered 16-byte fetches per bounce cheaper.
+//   tab[2 i]     = (Ld.x, Ld.y, Ld.z, -)             read where the reference calls SampleHdr
+//   tab[2 i + 1] = (hdrColor(Ld).rgb, hdrPdf(Ld))    read only when the shadow ray misses (same 32-byte sector)
+template <class M>
+__global__ void light_table_kernel(const DevScene sc, float4* __restrict__ tab) {
+    const size_t n = (size_t)sc.hdrW * sc.hdrH;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const V3 Ld = hdr_entry_direction(ldg4(sc.cache4 + i));
+        float u, w;
+        spherical_uv(Ld, u, w);
+        const float4 c = tex_nearest(sc.hdr4, sc.hdrW, sc.hdrH, u, w);
+        tab[2 * i] = make_float4(Ld.x, Ld.y, Ld.z, 0.0f);
+        tab[2 * i + 1] = make_float4(c.x, c.y, c.z, hdr_pdf<M>(sc, u, w));
+    }
+}
+template <class Cfg>
+cudaError_t build_light_table(const DevScene& sc, float4* tab, cudaStream_t stream) {
+    light_table_kernel<typename Cfg::M><<<148 * 8, 256, 0, stream>>>(sc, tab);
+    return cudaGetLastError();
 }
 
 // ---- Disney terms -------------------------------------------------------------------------------------
@@ -379,13 +408,21 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
     V3 fl = mk3(0, 0, 0), nextL = mk3(0, 0, 0);       // shadow phase: BRDF value toward the light; the pending bounce ray
     float ndl = 0.0f, pdf_b = 0.0f;                   //               N.Ld and the BRDF's pdf of Ld
     bool next_ok = false;
+    uint32_t light_idx = 0;                           // hdrCache texel of the light sample in flight (Cfg::LIGHT_TAB)
     int bounce = -1;
     int phase = PT_PH_PRIMARY;
     primary_id = -1;
     while (true) {
         const TraceResult tr = trace<Cfg>(sc, o, d, phase == PT_PH_SHADOW, cnt);
         nrays++;
-        if (tr.tri < 0) {
+        if (VARIANT == 2 && Cfg::LIGHT_TAB && tr.tri < 0 && phase == PT_PH_SHADOW) {
+            // ---- the shadow ray reached the environment: colour and pdf of its texel come from the light table (P:781-792) ----
+            const float4 e = ldg4(sc.light_tab + 2 * (size_t)light_idx + 1);
+            cnt.texel(2u);
+            const float pdf_light = e.w;
+            const float mis_weight = misMixWeight(pdf_light, pdf_b);
+            Lo = Lo + (history * mis_weight) * mk3(e.x, e.y, e.z) * fl * ndl / pdf_light;
+        } else if (tr.tri < 0) {
             // ---- the ray left the scene: one environment lookup serves all three phases ----
             float u, w;
             spherical_uv(d, u, w);
@@ -395,7 +432,7 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
             if (VARIANT == 2) {
                 const V3 color = mk3(c.x, c.y, c.z);                                                  // hdrColor, P:647-651
                 const float pdf_light = hdr_pdf<M>(sc, u, w);                                         // hdrPdf, P:655-666
-                if (phase == PT_PH_SHADOW) {                                                          // P:781-792
+                if (!Cfg::LIGHT_TAB && phase == PT_PH_SHADOW) {                                       // P:781-792
                     const float mis_weight = misMixWeight(pdf_light, pdf_b);
                     Lo = Lo + (history * mis_weight) * color * fl * ndl / pdf_light;
                 } else {                                                                              // P:819-830
@@ -431,7 +468,14 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
                 // light sampling through the hdrCache, P:770-775: the shadow ray flies first, the BRDF ray waits
                 const float e1 = rnd(seed);
                 const float e2 = rnd(seed);
-                const V3 Ld = SampleHdr<M>(sc, e1, e2);
+                V3 Ld;
+                if (Cfg::LIGHT_TAB) {
+                    light_idx = (uint32_t)nearest_texel(e2, sc.hdrH) * (uint32_t)sc.hdrW + (uint32_t)nearest_texel(e1, sc.hdrW);
+                    const float4 r0 = ldg4(sc.light_tab + 2 * (size_t)light_idx);
+                    Ld = mk3(r0.x, r0.y, r0.z);
+                } else {
+                    Ld = SampleHdr<M>(sc, e1, e2);
+                }
                 cnt.texel(1u);
                 ndl = dot(N, Ld);
                 const bool want_shadow = ndl > 0.0f;
@@ -559,6 +603,33 @@ __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
     asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// Tagged fold (PT_FOLD_TAGGED, default): the frame a pixel is ready for travels in the .w of the pixel's own float4, so
+// the "flag" and the data are ONE aligned 16-byte word — written by one st.relaxed.gpu.v4 and read by one
+// ld.relaxed.gpu.v4, each a single L2 transaction (the same single-copy property NCCL's LL protocols rest on).  No fence,
+// no release/acquire pair, no warp barrier and no separate progress array: the poll IS the accumulator read.
+// Within a launch w = PT_TAG | (next frame index of the launch); the launch's last frame stores w = 1 (the reference's
+// alpha, P:871); the first frame of a launch waits for nothing (kernel boundary).  A NaN pattern cannot collide with the
+// 1.0f / 0.0f a finished or cleared framebuffer holds.
+#ifndef PT_FOLD_TAGGED
+#define PT_FOLD_TAGGED 1
+#endif
+#define PT_TAG 0xffc00000u
+#ifndef PT_FOLD_PREFETCH
+#define PT_FOLD_PREFETCH 0
+#endif
+#ifndef PT_ITEM_FRAMES
+#define PT_ITEM_FRAMES 1           // consecutive frames of a tile computed by one claim and folded together
+#endif
+__device__ __forceinline__ uint4 ld_relaxed_v4(const float4* p) {
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_v4(float4* p, float x, float y, float z, uint32_t w) {
+    asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(__float_as_uint(x)), "r"(__float_as_uint(y)),
+                 "r"(__float_as_uint(z)), "r"(w) : "memory");
+}
+
 #define PT_PERSIST_CHUNK 1              // (tile, frame) items claimed per atomic
 #ifndef PT_PERSIST_MIN_CTAS
 #define PT_PERSIST_MIN_CTAS 5           // measured on B200 (is-1M / lambert-100k / disney-1M, Grays/s): 3 CTAs 11.6/5.7/5.3, 4: 12.4/6.5/6.1, 6: 12.6/7.0/6.8, 8: 12.1/6.9/6.7
@@ -568,7 +639,12 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
     const int lane = threadIdx.x & 31;
     const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
     const uint32_t ntiles = tm.count();                // owned 8x4 warp tiles
+#if PT_FOLD_TAGGED
+    const uint32_t ngroups = (p.n_frames + PT_ITEM_FRAMES - 1u) / PT_ITEM_FRAMES;   // an item = PT_ITEM_FRAMES consecutive frames of one tile
+    const uint32_t nitems = ntiles * ngroups;
+#else
     const uint32_t nitems = ntiles * p.n_frames;
+#endif
     // Order of the tile rows inside a frame: S passes over the rows a, a + S, a + 2S, ... (a = 0 .. S-1) instead of bottom to
     // top.  On the metric scene the lower half of the image is floor (three rays and two BRDF evaluations per sample: issue
     // bound) and the upper half sky (one trivial ray: bound by the framebuffer stream); bottom to top, the resident warps
@@ -580,6 +656,7 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
     S = min(S, max(1u, (uint32_t)tm.rows));
     uint32_t* head = p.sched;                          // [0] = next item; progress starts 64 words in
     uint32_t* progress = p.sched + 64;
+    (void)progress;
     uint32_t nrays = 0;
     Counter<Cfg::COUNT> cnt;
     for (;;) {
@@ -603,6 +680,57 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
             const int px = p.x0 + tx * 8 + (lane & 7);
             const int py = p.y0 + strip * 4 + (lane >> 3);
             const bool valid = px < p.x1 && py < p.y1;
+#if PT_FOLD_TAGGED
+            const long long t_start = p.cost ? clock64() : 0;
+            const uint32_t fa = f * PT_ITEM_FRAMES;         // first frame (index within the launch) of this item
+            const uint32_t nk = min((uint32_t)PT_ITEM_FRAMES, p.n_frames - fa);
+            V3 c[PT_ITEM_FRAMES];
+            int primary = -1;
+#if PT_FOLD_PREFETCH
+            if (valid) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.accum + (size_t)py * p.width + px));
+#endif
+#pragma unroll 1
+            for (uint32_t k2 = 0; k2 < nk; k2++) {
+                const uint32_t frame = p.first_frame + (fa + k2) * p.frame_stride;
+                V3 ck = mk3(0, 0, 0);
+                if (valid) ck = shade_sample<Cfg, VARIANT>(p, px, py, frame, p.sobol_tab ? p.sobol_tab + (size_t)(fa + k2) * 8 : nullptr, primary, nrays, cnt);
+                if (PT_ITEM_FRAMES == 1) c[0] = ck; else c[k2] = ck;
+            }
+            // ordered accumulation
+            if (valid) {
+                float4* const slot = p.accum + (size_t)py * p.width + px;
+                uint4 raw = ld_relaxed_v4(slot);
+                if (fa != 0u) {
+                    const uint32_t want = PT_TAG | (fa & 0x3fffffu);
+                    while (raw.w != want) { __nanosleep(32); raw = ld_relaxed_v4(slot); }
+                }
+                if (p.cost) __threadfence();               // profiling hook only: the cost word rides behind the tag
+                float ax = __uint_as_float(raw.x), ay = __uint_as_float(raw.y), az = __uint_as_float(raw.z);
+#pragma unroll
+                for (uint32_t k2 = 0; k2 < PT_ITEM_FRAMES; k2++) {
+                    if (k2 >= nk) break;
+                    if (p.accumulate_sum) {
+                        ax = s_add(ax, c[k2].x); ay = s_add(ay, c[k2].y); az = s_add(az, c[k2].z);
+                    } else {
+                        // mix(lastColor, color, 1/(frameCounter+1)), P:868-869, in the reference's frame order
+                        const float a = s_div(1.0f, (float)(p.first_frame + (fa + k2) * p.frame_stride + 1u));
+                        const float b = s_sub(1.0f, a);
+                        ax = s_add(s_mul(ax, b), s_mul(c[k2].x, a));
+                        ay = s_add(s_mul(ay, b), s_mul(c[k2].y, a));
+                        az = s_add(s_mul(az, b), s_mul(c[k2].z, a));
+                    }
+                }
+                const size_t idx = (size_t)py * p.width + px;
+                const bool last = fa + nk == p.n_frames;
+                if (last && p.primary_ids) p.primary_ids[idx] = primary;
+                if (p.cost) {
+                    const unsigned dt = (unsigned)(clock64() - t_start);
+                    __stcg(p.cost + idx, fa == 0 ? dt : __ldcg(p.cost + idx) + dt);
+                    __threadfence();
+                }
+                st_relaxed_v4(slot, ax, ay, az, last ? 0x3f800000u : (PT_TAG | ((fa + nk) & 0x3fffffu)));
+            }
+#else
             const uint32_t frame = p.first_frame + f * p.frame_stride;
             const long long t_start = p.cost ? clock64() : 0;
             V3 c = mk3(0, 0, 0);
@@ -634,6 +762,7 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
             // publish: the warp barrier orders every lane's store before lane 0's release store, and release is cumulative
             __syncwarp();
             if (lane == 0) st_release_u32(progress + tile, f + 1);
+#endif
         }
     }
     for (int o = 16; o > 0; o >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o);

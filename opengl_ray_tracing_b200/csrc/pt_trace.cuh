@@ -80,10 +80,21 @@ __device__ __forceinline__ bool hit_triangle(const Ray& r, V3 p1, V3 p2, V3 p3, 
 // candidate, with hit_aabb.  1/d is clamped to +-1e18 here: with an infinite 1/d the fused form gives inf - inf = NaN on
 // BOTH planes of a slab the origin lies in, and the NaN-dropping min/max would then reject a ray that passes.
 struct CullRay { V3 inv, noi; };                      // clamped 1/d and -(o * that)
-__device__ __forceinline__ CullRay make_cull_ray(const Ray& r) {
+// The culling reciprocal is the SFU's (rcp.approx: one instruction, 1 ulp) rather than the correctly rounded one: a
+// relative 2^-23 on every slab distance, again far inside the padding and the 2^-16 slack on `cull`.  The exact 1/d of the
+// reference's hitAABB is computed only for the rare candidate that reaches the leaf-box test (PT_LAZY_INV).
+#ifndef PT_LAZY_INV
+#define PT_LAZY_INV 1
+#endif
+__device__ __forceinline__ float rcp_approx(float a) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+}
+__device__ __forceinline__ CullRay make_cull_ray(V3 o, V3 inv) {
     CullRay c;
-    c.inv = mk3(fminf(fmaxf(r.inv.x, -1e18f), 1e18f), fminf(fmaxf(r.inv.y, -1e18f), 1e18f), fminf(fmaxf(r.inv.z, -1e18f), 1e18f));
-    c.noi = mk3(-s_mul(r.o.x, c.inv.x), -s_mul(r.o.y, c.inv.y), -s_mul(r.o.z, c.inv.z));
+    c.inv = mk3(fminf(fmaxf(inv.x, -1e18f), 1e18f), fminf(fmaxf(inv.y, -1e18f), 1e18f), fminf(fmaxf(inv.z, -1e18f), 1e18f));
+    c.noi = mk3(-s_mul(o.x, c.inv.x), -s_mul(o.y, c.inv.y), -s_mul(o.z, c.inv.z));
     return c;
 }
 __device__ __forceinline__ bool slab_cull_fused(const CullRay& c, V3 AA, V3 BB, float cull, float& entry) {
@@ -281,8 +292,13 @@ template <> struct Counter<false> {
 // ref is a leaf; test its triangles; pop.  Leaves travel through the stack like inner nodes.
 template <int STACK, class CNT>
 __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin, V3 dir, const bool anyhit, CNT& cnt) {
+#if PT_LAZY_INV
+    Ray r; r.o = origin; r.d = dir;                   // r.inv stays unset: hit_triangle does not read it
+    const CullRay cr = make_cull_ray(origin, mk3(rcp_approx(dir.x), rcp_approx(dir.y), rcp_approx(dir.z)));
+#else
     Ray r = make_ray(origin, dir);
-    const CullRay cr = make_cull_ray(r);
+    const CullRay cr = make_cull_ray(r.o, r.inv);
+#endif
     TraceResult res; res.tri = -1; res.t = PT_INF; res.inside = false;
     float cull = PT_INF;
     bool tie = false;
@@ -329,6 +345,9 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
                     if (meta.y != 1) {                // the reference never box-tests its root (P:342-343)
                         const float* nd = sc.nodes_raw + 12 * (size_t)meta.y;
                         float e;
+#if PT_LAZY_INV
+                        r.inv = mk3(s_rcp(dir.x), s_rcp(dir.y), s_rcp(dir.z));
+#endif
                         if (!(hit_aabb(r, raw3(nd + 6), raw3(nd + 9), e) > 0.0f)) continue;
                     }
                     if (!anyhit && tt == res.t) { tie = true; continue; }

@@ -13,7 +13,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libpt.so")
+# PT_LIBPT: load another BUILD of the same CUDA library (tools/build_variant.py: kernel A/B measurements)
+_LIB_PATH = os.environ.get("PT_LIBPT") or os.path.join(_HERE, "libpt.so")
 _lib = None
 
 LAMBERT, DISNEY_UNIFORM, DISNEY_IS_MIS = 0, 1, 2

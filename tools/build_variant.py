@@ -1,0 +1,23 @@
+"""Builds libpt_<name>.so next to libpt.so with extra -D macros on the two kernel translation units (A/B
+measurements of kernel variants in ONE gpurun call: PT_LIBPT=<path> selects the build at run time).
+
+    python tools/build_variant.py oldfold -DPT_FOLD_TAGGED=0
+"""
+import os, subprocess, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from opengl_ray_tracing_b200 import build as B
+
+name, defs = sys.argv[1], sys.argv[2:]
+B.build_pt()
+vdir = os.path.join(B.BUILD, "variant_" + name)
+os.makedirs(vdir, exist_ok=True)
+objs = []
+for unit, extra in (("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", ["-prec-div=false", "-prec-sqrt=false"])):
+    obj = os.path.join(vdir, unit + ".o")
+    B._run(["nvcc", *B.ARCH, *B.NVCC_COMMON, *extra, *defs, "-c", os.path.join(B.CSRC, unit + ".cu"), "-o", obj], log=os.path.join(vdir, unit + ".ptxas.log"))
+    objs.append(obj)
+objs += [os.path.join(B.BUILD, u + ".o") for u in ("pt_api", "pt_hdrcache", "pt_basic", "pt_build")]
+out = os.path.join(B.HERE, "libpt_%s.so" % name)
+B._run(["nvcc", *B.ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-lgomp", "-o", out])
+print(out)
