@@ -71,7 +71,7 @@ def build_pt(force=False):
         objs.append(obj)
     src, obj = os.path.join(CSRC, "pt_build.cpp"), os.path.join(BUILD, "pt_build.o")
     if force or _stale(obj, [src]):
-        _run(["g++", "-std=c++17", "-O3", "-fopenmp", "-fPIC", "-Wall", "-Wextra", "-c", src, "-o", obj])
+        _run(["g++", "-std=c++17", "-O3", "-ffp-contract=off", "-fopenmp", "-fPIC", "-Wall", "-Wextra", "-c", src, "-o", obj])
     objs.append(obj)
     out = os.path.join(HERE, "libpt.so")
     if force or _stale(out, objs):

@@ -25,6 +25,12 @@ static __constant__ uint32_t c_sobol_v[8 * 32] = {
 #include "pt_sobol_v.inc"
 };
 
+#ifndef PT_LIGHT_TAB
+#define PT_LIGHT_TAB 1            // light samples through the per-texel table (below)
+#endif
+#ifndef PT_SBRDF_MERGED
+#define PT_SBRDF_MERGED 1        // SampleBRDF with one toNormalHemisphere site
+#endif
 // ---- arithmetic configurations ------------------------------------------------------------------
 struct MathExact {                // include/ptmath.h: the oracle's definition of the GLSL transcendentals
     static __device__ __forceinline__ float sin(float a) { return pt_sinf(a); }
@@ -43,10 +49,10 @@ struct MathFast {                 // SFU approximations where CUDA has them
     static __device__ __forceinline__ float pow(float a, float b) { return __powf(a, b); }
 };
 struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = false; };
-struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = true; };
-struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true; };
-struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true; };
-struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  static const bool LIGHT_TAB = true; };
+struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = PT_LIGHT_TAB != 0; };
+struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = PT_LIGHT_TAB != 0; };
+struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = PT_LIGHT_TAB != 0; };
+struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  static const bool LIGHT_TAB = PT_LIGHT_TAB != 0; };
 
 // counting configuration: histogram of traversal steps (inner nodes + triangles) per ray, log2 buckets
 __device__ __forceinline__ uint32_t ray_steps(const Counter<false>&) { return 0; }
@@ -338,6 +344,36 @@ __device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 
     float r_sum = r_diffuse + r_specular + r_clearcoat;
     float p_diffuse = r_diffuse / r_sum, p_specular = r_specular / r_sum;
     float rd = xi_3;
+    // One toNormalHemisphere site for the three lobes (a warp on a glossy surface holds lanes of all of them): the branches
+    // only produce the local vector; the same operations in the same order per lane as the reference's three functions.
+#if PT_SBRDF_MERGED
+    V3 v;
+    bool half_vector = true;
+    if (rd <= p_diffuse) {                                        // SampleCosineHemisphere
+        float r = sqrtf(xi_1);
+        float theta = xi_2 * 2.0f * PT_PI;
+        float x = r * M::cos(theta), y = r * M::sin(theta);
+        v = mk3(x, y, sqrtf(1.0f - x * x - y * y));
+        half_vector = false;
+    } else {
+        float cos_theta_h;
+        if (p_diffuse < rd && rd <= p_diffuse + p_specular) {     // SampleGTR2
+            float alpha = alpha_GTR2;
+            cos_theta_h = sqrtf((1.0f - xi_2) / (1.0f + (alpha * alpha - 1.0f) * xi_2));
+        } else if (p_diffuse + p_specular < rd) {                 // SampleGTR1
+            float alpha = alpha_GTR1;
+            cos_theta_h = sqrtf((1.0f - M::pow(alpha * alpha, 1.0f - xi_2)) / (1.0f - alpha * alpha));
+        } else {
+            return mk3(0, 1, 0);                                  // only reachable through NaNs
+        }
+        float phi_h = 2.0f * PT_PI * xi_1;
+        float sin_phi_h = M::sin(phi_h), cos_phi_h = M::cos(phi_h);
+        float sin_theta_h = sqrtf(fmaxf(0.0f, 1.0f - cos_theta_h * cos_theta_h));
+        v = mk3(sin_theta_h * cos_phi_h, sin_theta_h * sin_phi_h, cos_theta_h);
+    }
+    const V3 w = toNormalHemisphere(v, N);
+    return half_vector ? reflect3(-V, w) : w;
+#else
     if (rd <= p_diffuse) {                                        // SampleCosineHemisphere
         float r = sqrtf(xi_1);
         float theta = xi_2 * 2.0f * PT_PI;
@@ -361,6 +397,7 @@ __device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 
     V3 H = mk3(sin_theta_h * cos_phi_h, sin_theta_h * sin_phi_h, cos_theta_h);
     H = toNormalHemisphere(H, N);
     return reflect3(-V, H);
+#endif
 }
 
 // ray generation, P:846-850, in strict arithmetic (primary-hit ids must be bit-exact in every mode).
