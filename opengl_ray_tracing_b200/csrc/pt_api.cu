@@ -35,6 +35,8 @@ cudaError_t hdr_cache_device(const float* d_rgb, int W, int H, float4* d_cache4,
 cudaError_t launch_fast(const RenderParams& p, int variant, bool count, cudaStream_t stream);
 cudaError_t build_light_table_parity(const DevScene& sc, float4* tab, cudaStream_t stream);   // pt_kernels_parity.cu
 cudaError_t build_light_table_fast(const DevScene& sc, float4* tab, cudaStream_t stream);     // pt_kernels_fast.cu
+cudaError_t derive_materials_parity(float4* materials, int n, cudaStream_t stream);
+cudaError_t derive_materials_fast(float4* materials, int n, cudaStream_t stream);
 cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
 cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
 cudaError_t launch_persistent_parity(const RenderParams& p, int variant, int which, int grid, cudaStream_t stream);
@@ -362,11 +364,12 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
                 const float rec[16] = {f[0], f[1], f[2], f[6], f[3], f[4], f[5], f[7],
                                        f[8], f[9], f[10], f[11], f[12], f[13], f[14], f[15]};
                 mat_table.insert(mat_table.end(), rec, rec + 16);
+                mat_table.insert(mat_table.end(), 16, 0.0f);     // derived half, filled on the device (material_derive_kernel)
             } else id = it->second;
             mat_id[i] = id; last = k; last_id = id;
         }
     }
-    const int nMaterials = (int)(mat_table.size() / 16);
+    const int nMaterials = (int)(mat_table.size() / 32);
 
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaStreamSynchronize(c->stream));
@@ -438,8 +441,11 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         CKU(cudaGetLastError());
         CKU(cudaStreamSynchronize(st));               // ft goes out of scope
     }
-    CKU(cudaMalloc(&c->materials, (size_t)nMaterials * 4 * sizeof(float4)));
-    CKU(cudaMemcpyAsync(c->materials, mat_table.data(), (size_t)nMaterials * 16 * sizeof(float), cudaMemcpyHostToDevice, st));
+    CKU(cudaMalloc(&c->materials, (size_t)nMaterials * 8 * sizeof(float4)));
+    CKU(cudaMemcpyAsync(c->materials, mat_table.data(), (size_t)nMaterials * 32 * sizeof(float), cudaMemcpyHostToDevice, st));
+    // second half of each record: what the Disney functions derive from the material alone, in this context's arithmetic
+    CKU((c->cfg.mode == PT_MODE_FAST || c->cfg.mode == PT_MODE_FAST_COUNT) ? pt::derive_materials_fast(c->materials, nMaterials, st)
+                                                                          : pt::derive_materials_parity(c->materials, nMaterials, st));
     // environment
     CKU(cudaMalloc(&d_tmp, ntex * 3 * sizeof(float)));
     CKU(cudaMalloc(&c->hdr4, ntex * sizeof(float4)));
@@ -481,7 +487,7 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
             c->launches += 1;
         }
         c->has_scene = true;
-        c->launches += 5 + (hdrCache ? 1 : cache_launches);
+        c->launches += 6 + (hdrCache ? 1 : cache_launches);
         // Optional L2 persistence window over the production tree's nodes (north star item 2); PT_L2_WINDOW_MB=0 (default)
         // leaves L2 to its own replacement: measured no gain, DESIGN.md §7.
         if (const char* e = std::getenv("PT_L2_WINDOW_MB")) {

@@ -80,7 +80,7 @@ struct DevScene {
     const int2* trimeta;        // per re-ordered triangle: (uploaded triangle index, reference leaf node holding it)
     const float4* trigeo;       // nTriangles x 3 float4 (48 B): (p1,N.x) (p2,N.y) (p3,N.z), N = unit face normal
     const float4* trishade;     // nTriangles x 3 float4 (48 B): (n1, matId) (n2, -) (n3, -)
-    const float4* materials;    // nMaterials x 4 float4 (64 B)
+    const float4* materials;    // nMaterials x 8 float4 (128 B): the 16 parameters, then 16 values derived from them (pt_shade.cuh MaterialD)
     const float4* hdr4;         // hdrH x hdrW float4 (rgb, 0)
     const float4* cache4;       // hdrH x hdrW float4 (x/w, y/h, pdf, 0) or null
     const float4* light_tab;    // hdrH x hdrW x 2 float4: what a light sample through each cache texel evaluates to (pt_shade.cuh) or null

@@ -17,4 +17,5 @@ cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count
     return launch_wavefront<CfgFast>(p, variant, grid, stream);
 }
 cudaError_t build_light_table_fast(const DevScene& sc, float4* tab, cudaStream_t stream) { return build_light_table<CfgFast>(sc, tab, stream); }
+cudaError_t derive_materials_fast(float4* materials, int n, cudaStream_t stream) { return derive_materials<CfgFast>(materials, n, stream); }
 }  // namespace pt

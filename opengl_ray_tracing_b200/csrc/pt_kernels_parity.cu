@@ -22,4 +22,5 @@ cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int whic
     return launch_wavefront<CfgParityFast>(p, variant, grid, stream);
 }
 cudaError_t build_light_table_parity(const DevScene& sc, float4* tab, cudaStream_t stream) { return build_light_table<CfgParityWide>(sc, tab, stream); }
+cudaError_t derive_materials_parity(float4* materials, int n, cudaStream_t stream) { return derive_materials<CfgParityWide>(materials, n, stream); }
 }  // namespace pt

@@ -225,16 +225,110 @@ __device__ __forceinline__ float SchlickFresnel(float u) {
     float m2 = m * m;
     return m2 * m2 * m;
 }
-template <class M> __device__ __forceinline__ float GTR1(float NdotH, float a) {
-    if (a >= 1.0f) return 1.0f / PT_PI;
-    float a2 = a * a;
-    float t = 1.0f + (a2 - 1.0f) * NdotH * NdotH;
-    return (a2 - 1.0f) / (PT_PI * M::log(a2) * t);
+// What the Disney functions compute from the MATERIAL ALONE — the tinted specular colours of P:436-441, the lobe
+// probabilities of P:547-553 / P:690-699, the two GTR widths with their squares and PI*log(a^2) of P:398-404, the anisotropic
+// widths of P:456-458 — is the same for every evaluation of that material: ~145 instructions per bounce on the metric scene.
+// MaterialD reads those values from the second half of the material's 128-byte record, where the upload evaluated the very
+// same expressions in the context's arithmetic (material_derive_kernel); a plain Material (PT_MODE_PARITY_REF, whose
+// materials live in the triangle records, and the wavefront stages) evaluates them in place.  Same values bit for bit.
+struct MatSpec { V3 Cspec0, Csheen; };
+struct MatLobes { float p_diffuse, p_specular, p_clearcoat; };
+struct MatGtr { float alpha1, a2m1_1, pilog_1, a2_2, a2m1_2; };   // clearcoat GTR1: a, a^2 - 1, PI log(a^2); specular GTR2: a^2, a^2 - 1
+struct MatAniso { float ax, ay; };
+struct MaterialD : Material { const float4* ext; };               // ext = the record's derived half (4 float4)
+
+template <class M> __device__ __forceinline__ MatSpec mat_spec(const Material& mt) {                       // P:436-441
+    MatSpec r;
+    V3 Cdlin = mt.baseColor;
+    float Cdlum = 0.3f * Cdlin.x + 0.6f * Cdlin.y + 0.1f * Cdlin.z;
+    V3 Ctint = (Cdlum > 0.0f) ? (Cdlin / Cdlum) : mk3(1, 1, 1);
+    V3 Cspec = mix3(mk3(1, 1, 1), Ctint, mt.specularTint) * mt.specular;
+    r.Cspec0 = mix3(Cspec * 0.08f, Cdlin, mt.metallic);
+    r.Csheen = mix3(mk3(1, 1, 1), Ctint, mt.sheenTint);
+    return r;
 }
-__device__ __forceinline__ float GTR2(float NdotH, float a) {
-    float a2 = a * a;
-    float t = 1.0f + (a2 - 1.0f) * NdotH * NdotH;
-    return a2 / (PT_PI * t * t);
+template <class M> __device__ __forceinline__ MatLobes mat_lobes(const Material& mt) {                     // P:547-553
+    float r_diffuse = (1.0f - mt.metallic), r_specular = 1.0f, r_clearcoat = 0.25f * mt.clearcoat;
+    float r_sum = r_diffuse + r_specular + r_clearcoat;
+    MatLobes r;
+    r.p_diffuse = r_diffuse / r_sum; r.p_specular = r_specular / r_sum; r.p_clearcoat = r_clearcoat / r_sum;
+    return r;
+}
+template <class M> __device__ __forceinline__ MatGtr mat_gtr(const Material& mt) {
+    MatGtr r;
+    r.alpha1 = mixf(0.1f, 0.001f, mt.clearcoatGloss);
+    float a2 = r.alpha1 * r.alpha1;
+    r.a2m1_1 = a2 - 1.0f;
+    r.pilog_1 = PT_PI * M::log(a2);
+    float alpha2 = fmaxf(0.001f, sqr(mt.roughness));
+    r.a2_2 = alpha2 * alpha2;
+    r.a2m1_2 = r.a2_2 - 1.0f;
+    return r;
+}
+template <class M> __device__ __forceinline__ MatAniso mat_aniso(const Material& mt) {                    // P:456-458
+    float aspect = sqrtf(1.0f - mt.anisotropic * 0.9f);
+    MatAniso r;
+    r.ax = fmaxf(0.001f, sqr(mt.roughness) / aspect);
+    r.ay = fmaxf(0.001f, sqr(mt.roughness) * aspect);
+    return r;
+}
+// derived half of the record: (Cspec0, a2_2) (Csheen, alpha1) (p_diffuse, p_specular, p_clearcoat, a2m1_2) (a2m1_1, pilog_1, ax, ay)
+template <class M> __device__ __forceinline__ MatSpec mat_spec(const MaterialD& mt) {
+    const float4 a = ldg4(mt.ext), b = ldg4(mt.ext + 1);
+    MatSpec r; r.Cspec0 = mk3(a.x, a.y, a.z); r.Csheen = mk3(b.x, b.y, b.z);
+    return r;
+}
+template <class M> __device__ __forceinline__ MatLobes mat_lobes(const MaterialD& mt) {
+    const float4 c = ldg4(mt.ext + 2);
+    MatLobes r; r.p_diffuse = c.x; r.p_specular = c.y; r.p_clearcoat = c.z;
+    return r;
+}
+template <class M> __device__ __forceinline__ MatGtr mat_gtr(const MaterialD& mt) {
+    const float4 a = ldg4(mt.ext), b = ldg4(mt.ext + 1), c = ldg4(mt.ext + 2), d = ldg4(mt.ext + 3);
+    MatGtr r; r.alpha1 = b.w; r.a2m1_1 = d.x; r.pilog_1 = d.y; r.a2_2 = a.w; r.a2m1_2 = c.w;
+    return r;
+}
+template <class M> __device__ __forceinline__ MatAniso mat_aniso(const MaterialD& mt) {
+    const float4 d = ldg4(mt.ext + 3);
+    MatAniso r; r.ax = d.z; r.ay = d.w;
+    return r;
+}
+// one thread per material: the derived half of each 128-byte record, in the arithmetic of the translation unit
+template <class M>
+__global__ void material_derive_kernel(float4* __restrict__ materials, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4* p = materials + 8 * (size_t)i;
+    const float4 a = p[0], b = p[1], c = p[2], d = p[3];
+    Material m;
+    m.emissive = mk3(a.x, a.y, a.z); m.subsurface = a.w;
+    m.baseColor = mk3(b.x, b.y, b.z); m.metallic = b.w;
+    m.specular = c.x; m.specularTint = c.y; m.roughness = c.z; m.anisotropic = c.w;
+    m.sheen = d.x; m.sheenTint = d.y; m.clearcoat = d.z; m.clearcoatGloss = d.w;
+    const MatSpec sp = mat_spec<M>(m);
+    const MatLobes lb = mat_lobes<M>(m);
+    const MatGtr g = mat_gtr<M>(m);
+    const MatAniso an = mat_aniso<M>(m);
+    p[4] = make_float4(sp.Cspec0.x, sp.Cspec0.y, sp.Cspec0.z, g.a2_2);
+    p[5] = make_float4(sp.Csheen.x, sp.Csheen.y, sp.Csheen.z, g.alpha1);
+    p[6] = make_float4(lb.p_diffuse, lb.p_specular, lb.p_clearcoat, g.a2m1_2);
+    p[7] = make_float4(g.a2m1_1, g.pilog_1, an.ax, an.ay);
+}
+template <class Cfg>
+cudaError_t derive_materials(float4* materials, int n, cudaStream_t stream) {
+    material_derive_kernel<typename Cfg::M><<<(n + 127) / 128, 128, 0, stream>>>(materials, n);
+    return cudaGetLastError();
+}
+
+// GTR1 (P:398-404) and GTR2 (P:406-410) on the derived widths
+__device__ __forceinline__ float GTR1(float NdotH, const MatGtr& g) {
+    if (g.alpha1 >= 1.0f) return 1.0f / PT_PI;
+    float t = 1.0f + g.a2m1_1 * NdotH * NdotH;
+    return g.a2m1_1 / (g.pilog_1 * t);
+}
+__device__ __forceinline__ float GTR2(float NdotH, const MatGtr& g) {
+    float t = 1.0f + g.a2m1_2 * NdotH * NdotH;
+    return g.a2_2 / (PT_PI * t * t);
 }
 __device__ __forceinline__ float GTR2_aniso(float NdotH, float HdotX, float HdotY, float ax, float ay) {
     return 1.0f / (PT_PI * ax * ay * sqr(sqr(HdotX / ax) + sqr(HdotY / ay) + NdotH * NdotH));
@@ -252,17 +346,16 @@ struct DisneyCommon {
     V3 Cdlin, Cspec0, Csheen;
     float Fd, ss, FH, NdotH, LdotH;
 };
-__device__ __forceinline__ DisneyCommon disney_common(V3 V, V3 N, V3 L, float NdotL, float NdotV, const Material& mt) {
+template <class M, class MT>
+__device__ __forceinline__ DisneyCommon disney_common(V3 V, V3 N, V3 L, float NdotL, float NdotV, const MT& mt) {
     DisneyCommon c;
     V3 H = normalize(L + V);
     c.NdotH = dot(N, H);
     c.LdotH = dot(L, H);
     c.Cdlin = mt.baseColor;
-    float Cdlum = 0.3f * c.Cdlin.x + 0.6f * c.Cdlin.y + 0.1f * c.Cdlin.z;
-    V3 Ctint = (Cdlum > 0.0f) ? (c.Cdlin / Cdlum) : mk3(1, 1, 1);
-    V3 Cspec = mix3(mk3(1, 1, 1), Ctint, mt.specularTint) * mt.specular;
-    c.Cspec0 = mix3(Cspec * 0.08f, c.Cdlin, mt.metallic);
-    c.Csheen = mix3(mk3(1, 1, 1), Ctint, mt.sheenTint);
+    const MatSpec sp = mat_spec<M>(mt);
+    c.Cspec0 = sp.Cspec0;
+    c.Csheen = sp.Csheen;
     float Fd90 = 0.5f + 2.0f * c.LdotH * c.LdotH * mt.roughness;
     float FL = SchlickFresnel(NdotL), FV = SchlickFresnel(NdotV);
     c.Fd = mixf(1.0f, Fd90, FL) * mixf(1.0f, Fd90, FV);
@@ -272,12 +365,12 @@ __device__ __forceinline__ DisneyCommon disney_common(V3 V, V3 N, V3 L, float Nd
     c.FH = SchlickFresnel(c.LdotH);
     return c;
 }
-template <class M>
-__device__ __forceinline__ V3 disney_combine(const DisneyCommon& c, float Gs, float Ds, float NdotL, float NdotV,
-                                             const Material& mt) {
+template <class M, class MT>
+__device__ __forceinline__ V3 disney_combine(const DisneyCommon& c, float Gs, float Ds, float NdotL, float NdotV, const MatGtr& g,
+                                             const MT& mt) {
     V3 Fs = mix3(c.Cspec0, mk3(1, 1, 1), c.FH);
     V3 specular = (Fs * Gs) * Ds;
-    float Dr = GTR1<M>(c.NdotH, mixf(0.1f, 0.001f, mt.clearcoatGloss));
+    float Dr = GTR1(c.NdotH, g);
     float Fr = mixf(0.04f, 1.0f, c.FH);
     float Gr = smithG_GGX(NdotL, 0.25f) * smithG_GGX(NdotV, 0.25f);
     float cc = 0.25f * Gr * Fr * Dr * mt.clearcoat;
@@ -287,62 +380,56 @@ __device__ __forceinline__ V3 disney_combine(const DisneyCommon& c, float Gs, fl
 }
 
 // BRDF_Evaluate_aniso P:423-482 (the Disney variant's BRDF_Evaluate, D:381-440)
-template <class M>
-__device__ __forceinline__ V3 BRDF_Evaluate_aniso(V3 V, V3 N, V3 L, V3 X, V3 Y, const Material& mt) {
+template <class M, class MT>
+__device__ __forceinline__ V3 BRDF_Evaluate_aniso(V3 V, V3 N, V3 L, V3 X, V3 Y, const MT& mt) {
     float NdotL = dot(N, L), NdotV = dot(N, V);
     if (NdotL < 0.0f || NdotV < 0.0f) return mk3(0, 0, 0);
-    DisneyCommon c = disney_common(V, N, L, NdotL, NdotV, mt);
+    DisneyCommon c = disney_common<M>(V, N, L, NdotL, NdotV, mt);
     V3 H = normalize(L + V);
-    float aspect = sqrtf(1.0f - mt.anisotropic * 0.9f);
-    float ax = fmaxf(0.001f, sqr(mt.roughness) / aspect);
-    float ay = fmaxf(0.001f, sqr(mt.roughness) * aspect);
-    float Ds = GTR2_aniso(c.NdotH, dot(H, X), dot(H, Y), ax, ay);
-    float Gs = smithG_GGX_aniso(NdotL, dot(L, X), dot(L, Y), ax, ay);
-    Gs *= smithG_GGX_aniso(NdotV, dot(V, X), dot(V, Y), ax, ay);
-    return disney_combine<M>(c, Gs, Ds, NdotL, NdotV, mt);
+    const MatAniso an = mat_aniso<M>(mt);
+    float Ds = GTR2_aniso(c.NdotH, dot(H, X), dot(H, Y), an.ax, an.ay);
+    float Gs = smithG_GGX_aniso(NdotL, dot(L, X), dot(L, Y), an.ax, an.ay);
+    Gs *= smithG_GGX_aniso(NdotV, dot(V, X), dot(V, Y), an.ax, an.ay);
+    return disney_combine<M>(c, Gs, Ds, NdotL, NdotV, mat_gtr<M>(mt), mt);
 }
 // isotropic BRDF_Evaluate of the IS shader, P:587-636 (smithG_GGX takes roughness, not alpha: P:620-621)
-template <class M>
-__device__ __forceinline__ V3 BRDF_Evaluate_iso(V3 V, V3 N, V3 L, const Material& mt) {
+template <class M, class MT>
+__device__ __forceinline__ V3 BRDF_Evaluate_iso(V3 V, V3 N, V3 L, const MT& mt) {
     float NdotL = dot(N, L), NdotV = dot(N, V);
     if (NdotL < 0.0f || NdotV < 0.0f) return mk3(0, 0, 0);
-    DisneyCommon c = disney_common(V, N, L, NdotL, NdotV, mt);
-    float alpha = fmaxf(0.001f, sqr(mt.roughness));
-    float Ds = GTR2(c.NdotH, alpha);
+    DisneyCommon c = disney_common<M>(V, N, L, NdotL, NdotV, mt);
+    const MatGtr g = mat_gtr<M>(mt);
+    float Ds = GTR2(c.NdotH, g);
     float Gs = smithG_GGX(NdotL, mt.roughness);
     Gs *= smithG_GGX(NdotV, mt.roughness);
-    return disney_combine<M>(c, Gs, Ds, NdotL, NdotV, mt);
+    return disney_combine<M>(c, Gs, Ds, NdotL, NdotV, g, mt);
 }
 
 // BRDF_Pdf, P:669-706
-template <class M> __device__ __forceinline__ float BRDF_Pdf(V3 V, V3 N, V3 L, const Material& mt) {
+template <class M, class MT> __device__ __forceinline__ float BRDF_Pdf(V3 V, V3 N, V3 L, const MT& mt) {
     float NdotL = dot(N, L), NdotV = dot(N, V);
     if (NdotL < 0.0f || NdotV < 0.0f) return 0.0f;
     V3 H = normalize(L + V);
     float NdotH = dot(N, H), LdotH = dot(L, H);
-    float alpha = fmaxf(0.001f, sqr(mt.roughness));
-    float Ds = GTR2(NdotH, alpha);
-    float Dr = GTR1<M>(NdotH, mixf(0.1f, 0.001f, mt.clearcoatGloss));
+    const MatGtr g = mat_gtr<M>(mt);
+    float Ds = GTR2(NdotH, g);
+    float Dr = GTR1(NdotH, g);
     float pdf_diffuse = NdotL / PT_PI;
     float pdf_specular = Ds * NdotH / (4.0f * LdotH);
     float pdf_clearcoat = Dr * NdotH / (4.0f * LdotH);
-    float r_diffuse = (1.0f - mt.metallic), r_specular = 1.0f, r_clearcoat = 0.25f * mt.clearcoat;
-    float r_sum = r_diffuse + r_specular + r_clearcoat;
-    float p_diffuse = r_diffuse / r_sum, p_specular = r_specular / r_sum, p_clearcoat = r_clearcoat / r_sum;
-    float pdf = p_diffuse * pdf_diffuse + p_specular * pdf_specular + p_clearcoat * pdf_clearcoat;
+    const MatLobes lb = mat_lobes<M>(mt);
+    float pdf = lb.p_diffuse * pdf_diffuse + lb.p_specular * pdf_specular + lb.p_clearcoat * pdf_clearcoat;
     return fmaxf(1e-10f, pdf);
 }
 __device__ __forceinline__ float misMixWeight(float a, float b) { float t = a * a; return t / (b * b + t); }
 
 // SampleBRDF, P:539-570 with its three lobe samplers P:485-536
 __device__ __forceinline__ V3 reflect3(V3 I, V3 N) { return I - N * (2.0f * dot(N, I)); }
-template <class M>
-__device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 V, V3 N, const Material& mt) {
-    float alpha_GTR1 = mixf(0.1f, 0.001f, mt.clearcoatGloss);
-    float alpha_GTR2 = fmaxf(0.001f, sqr(mt.roughness));
-    float r_diffuse = (1.0f - mt.metallic), r_specular = 1.0f, r_clearcoat = 0.25f * mt.clearcoat;
-    float r_sum = r_diffuse + r_specular + r_clearcoat;
-    float p_diffuse = r_diffuse / r_sum, p_specular = r_specular / r_sum;
+template <class M, class MT>
+__device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 V, V3 N, const MT& mt) {
+    const MatGtr g = mat_gtr<M>(mt);
+    const MatLobes lb = mat_lobes<M>(mt);
+    const float p_diffuse = lb.p_diffuse, p_specular = lb.p_specular;
     float rd = xi_3;
     // One toNormalHemisphere site for the three lobes (a warp on a glossy surface holds lanes of all of them): the branches
     // only produce the local vector; the same operations in the same order per lane as the reference's three functions.
@@ -358,11 +445,10 @@ __device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 
     } else {
         float cos_theta_h;
         if (p_diffuse < rd && rd <= p_diffuse + p_specular) {     // SampleGTR2
-            float alpha = alpha_GTR2;
-            cos_theta_h = sqrtf((1.0f - xi_2) / (1.0f + (alpha * alpha - 1.0f) * xi_2));
+            cos_theta_h = sqrtf((1.0f - xi_2) / (1.0f + g.a2m1_2 * xi_2));
         } else if (p_diffuse + p_specular < rd) {                 // SampleGTR1
-            float alpha = alpha_GTR1;
-            cos_theta_h = sqrtf((1.0f - M::pow(alpha * alpha, 1.0f - xi_2)) / (1.0f - alpha * alpha));
+            const float a2 = g.alpha1 * g.alpha1;
+            cos_theta_h = sqrtf((1.0f - M::pow(a2, 1.0f - xi_2)) / (1.0f - a2));
         } else {
             return mk3(0, 1, 0);                                  // only reachable through NaNs
         }
@@ -383,11 +469,10 @@ __device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 
     }
     float cos_theta_h;
     if (p_diffuse < rd && rd <= p_diffuse + p_specular) {         // SampleGTR2
-        float alpha = alpha_GTR2;
-        cos_theta_h = sqrtf((1.0f - xi_2) / (1.0f + (alpha * alpha - 1.0f) * xi_2));
+        cos_theta_h = sqrtf((1.0f - xi_2) / (1.0f + g.a2m1_2 * xi_2));
     } else if (p_diffuse + p_specular < rd) {                     // SampleGTR1
-        float alpha = alpha_GTR1;
-        cos_theta_h = sqrtf((1.0f - M::pow(alpha * alpha, 1.0f - xi_2)) / (1.0f - alpha * alpha));
+        const float a2 = g.alpha1 * g.alpha1;
+        cos_theta_h = sqrtf((1.0f - M::pow(a2, 1.0f - xi_2)) / (1.0f - a2));
     } else {
         return mk3(0, 1, 0);                                      // only reachable through NaNs
     }
@@ -415,6 +500,11 @@ __device__ __forceinline__ void generate_ray(const RenderParams& p, int px, int 
     d = s_normalize(d);
     o = mk3(p.eye[0], p.eye[1], p.eye[2]);
 }
+
+template <bool RAW> struct MatOf { typedef Material T; };
+template <> struct MatOf<false> { typedef MaterialD T; };
+__device__ __forceinline__ void set_ext(Material&, const DevScene&, int) {}
+__device__ __forceinline__ void set_ext(MaterialD& m, const DevScene& sc, int mat_id) { m.ext = sc.materials + 8 * (size_t)mat_id + 4; }
 
 // ---- one sample of one pixel: main() of the three shaders ------------------------------------------
 // Returns this frame's colour BEFORE accumulation; primary_id = triangle of the primary hit (-1 miss).
@@ -488,8 +578,9 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
             int mat_id;
             finalize_hit<Cfg::RAW>(sc, o, d, tr, hit, mat_id);
             cnt.shaded();
-            Material mat;
+            typename MatOf<Cfg::RAW>::T mat;
             load_material<Cfg::RAW>(sc, mat_id, mat);
+            set_ext(mat, sc, mat_id);
             if (phase == PT_PH_PRIMARY) {
                 primary_id = tr.tri;
                 Le0 = mat.emissive;                                                                   // P:862

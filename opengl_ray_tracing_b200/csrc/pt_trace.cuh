@@ -426,7 +426,7 @@ __device__ __forceinline__ void load_material(const DevScene& sc, int mat_id, Ma
         m.specularTint = ldg1(t + 9); m.roughness = ldg1(t + 10); m.anisotropic = ldg1(t + 11);
         m.sheen = ldg1(t + 12); m.sheenTint = ldg1(t + 13); m.clearcoat = ldg1(t + 14); m.clearcoatGloss = ldg1(t + 15);
     } else {
-        const float4* p = sc.materials + 4 * (size_t)mat_id;
+        const float4* p = sc.materials + 8 * (size_t)mat_id;      // 128-byte records: 4 float4 as uploaded, 4 derived (pt_shade.cuh)
         float4 a = ldg4(p), b = ldg4(p + 1), c = ldg4(p + 2), d = ldg4(p + 3);
         m.emissive = mk3(a.x, a.y, a.z); m.subsurface = a.w;
         m.baseColor = mk3(b.x, b.y, b.z); m.metallic = b.w;
