@@ -369,7 +369,7 @@ def run_ours(args):
                        "split": args.split if world > 1 else "none",
                        "l2": "flushed between steps (256 MiB fill)" if flush is not None else "not flushed",
                        "scene_bytes_hbm": int(sc.tris.nbytes + sc.nodes.nbytes + sc.nTriangles * 96 + st["n_inner_nodes"] * 64
-                                              + sc.hdr.shape[0] * sc.hdr.shape[1] * 16 * (2 if sc.hdrCache is not None else 1))},
+                                              + sc.hdr.shape[0] * sc.hdr.shape[1] * 16 * (4 if sc.hdrCache is not None else 1))},   # hdr4 (+ cache4 + 32 B light table)
             "spp_per_s": spp_per_s, "rays_per_sample": rays / max(1.0, samples),
             "e2e": {"value": e2e_mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": int(host.numel() * 4),
                     "ms_per_step": t_e2e / args.steps * 1e3},
@@ -402,7 +402,7 @@ def run_ours(args):
                             "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
                             "inner_per_ray": cs["inner_visits"] / max(1, cs["rays"]), "tris_per_ray": cs["tri_tests"] / max(1, cs["rays"]),
                             "shaded_hits_per_ray": cs["shaded_hits"] / max(1, cs["rays"]), "texels_per_ray": cs["env_texels"] / max(1, cs["rays"]),
-                            "kernel": "render_persistent<CfgFast,%d>" % sc.variant, "kernel_ms_per_launch": kern_ms / max(1, launches / world),
+                            "kernel": "render_persistent<CfgFast,%d>" % sc.variant, "kernel_ms_per_launch": kern_ms / args.steps,      # one render launch per step and rank (max over ranks)
                             "issue": issue,
                             "note": "the path is SM-issue/latency bound with an L2-resident working set (DESIGN.md); "
                                     "traffic = ncu dram bytes of one launch of the committed capture (profiles/)"}

@@ -759,11 +759,14 @@ __device__ __forceinline__ void st_relaxed_v4(float4* p, float x, float y, float
 }
 
 #define PT_PERSIST_CHUNK 1              // (tile, frame) items claimed per atomic
+#ifndef PT_PERSIST_THREADS
+#define PT_PERSIST_THREADS 256
+#endif
 #ifndef PT_PERSIST_MIN_CTAS
 #define PT_PERSIST_MIN_CTAS 5           // measured on B200 (is-1M / lambert-100k / disney-1M, Grays/s): 3 CTAs 11.6/5.7/5.3, 4: 12.4/6.5/6.1, 6: 12.6/7.0/6.8, 8: 12.1/6.9/6.7
 #endif
 template <class Cfg, int VARIANT>
-__global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(const __grid_constant__ RenderParams p) {
+__global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) render_persistent(const __grid_constant__ RenderParams p) {
     const int lane = threadIdx.x & 31;
     const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
     const uint32_t ntiles = tm.count();                // owned 8x4 warp tiles
@@ -780,7 +783,7 @@ __global__ void __launch_bounds__(256, PT_PERSIST_MIN_CTAS) render_persistent(co
     // (S = 8), +6.5 % at 4K (S = 32), the measured optimum at both; scenes without such a split (variants 0 and 1 here) are
     // neutral to -2.5 %, so the rule is applied to variant 2 only.  PT_SCHED_STRIDE overrides.  DESIGN.md §5.
     uint32_t S = p.sched_stride;
-    if (S == 0u) S = VARIANT == 2 ? max(1u, (uint32_t)(0.74f * (float)ntiles / (float)(gridDim.x * 8u) + 0.5f)) : 1u;
+    if (S == 0u) S = VARIANT == 2 ? max(1u, (uint32_t)(0.74f * (float)ntiles / (float)(gridDim.x * (PT_PERSIST_THREADS / 32u)) + 0.5f)) : 1u;
     S = min(S, max(1u, (uint32_t)tm.rows));
     uint32_t* head = p.sched;                          // [0] = next item; progress starts 64 words in
     uint32_t* progress = p.sched + 64;
@@ -910,12 +913,12 @@ cudaError_t launch_persistent(const RenderParams& p, int variant, int num_sms, c
     // one resident set of CTAs: SMs x (CTAs that fit per SM), never more warps than there are tiles
     void (*kern)(const RenderParams) = variant == 0 ? render_persistent<Cfg, 0> : variant == 1 ? render_persistent<Cfg, 1> : render_persistent<Cfg, 2>;
     int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PT_PERSIST_THREADS, 0);
     if (e != cudaSuccess) return e;
     int grid = num_sms * (per_sm > 0 ? per_sm : 1);
-    const int need = (int)((ntiles + 7) / 8);
+    const int need = (int)((ntiles + PT_PERSIST_THREADS / 32 - 1) / (PT_PERSIST_THREADS / 32));
     if (grid > need) grid = need;
-    kern<<<grid, 256, 0, stream>>>(p);
+    kern<<<grid, PT_PERSIST_THREADS, 0, stream>>>(p);
     return cudaGetLastError();
 }
 
