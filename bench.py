@@ -13,9 +13,10 @@ A step = `--spp` frames (samples per pixel) of the whole 1080p image.  Prints ON
                    triangle tested, 108 B per shaded hit, 32 B per sample, 12 B per environment texel; the per-ray
                    counts come from the counting build of the same kernel on one frame of the whole image) / launch time
   cpu_baseline     the CPU oracle (OpenMP, all host cores) on a bounded crop of the same workload
-N > 1 (torchrun, one rank per GPU): the scene is replicated, the image is split in interleaved 8-row bands
-(one launch per rank), and every step ends with an NCCL reduce of the framebuffers to rank 0 — total work is
-fixed, so "scaling" is "strong".
+N > 1 (torchrun, one rank per GPU): the scene is replicated, a step's frames are dealt round-robin to the ranks
+(--split sample: per-rank sums, one launch per rank) or the image is split in diagonal 8x4 tiles (--split tile:
+bit-identical to one GPU), and every step ends with an NCCL reduce of the framebuffers to rank 0 — total work
+is fixed, so "scaling" is "strong".
 """
 from __future__ import annotations
 
@@ -54,7 +55,10 @@ def parse_args():
     ap.add_argument("--workload", default="is-1M-1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=256, help="frames (samples per pixel) per step")
     ap.add_argument("--pipeline", type=int, default=2, help="0 megakernel, 1 wavefront, 2 persistent (production)")
-    ap.add_argument("--split", default="tile", choices=["tile", "sample"])
+    ap.add_argument("--split", default="sample", choices=["tile", "sample"],
+                    help="N > 1: sample = frames dealt round-robin, per-rank sums reduced and scaled (default: every rank keeps the "
+                         "whole image, so a tile's consecutive frames stay ~11 resident-warp generations apart, as on one GPU); "
+                         "tile = diagonal 8x4 tiles, bit-identical to one GPU")
     ap.add_argument("--mode", type=int, default=0, help="0 fast (production), 1 parity-ref, 2 parity-wide")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-l2-flush", action="store_true")
@@ -343,8 +347,12 @@ def run_ours(args):
         pt.set_camera(eye_h, cam_h)
         render_step(frame); frame += spp
         if world > 1:
-            torch.cuda.synchronize()
-        pt.readback_into(host.data_ptr(), host.numel() * 4)
+            if rank == 0:                              # the job's result is the combined image on rank 0
+                with torch.cuda.stream(stream):
+                    host.copy_(combined, non_blocking=True)
+            stream.synchronize()
+        else:
+            pt.readback_into(host.data_ptr(), host.numel() * 4)
     barrier()
     t_e2e = time.perf_counter() - t0
     st2 = pt.stats()

@@ -108,7 +108,10 @@ def combine(fb, out=None, dst: int = 0, scale: float | None = None, group=None):
     if multi:
         dist.reduce(out, dst=dst, op=dist.ReduceOp.SUM, group=group)
     if scale is not None and (not multi or dist.get_rank(group) == dst):
-        out[..., :3] *= scale
+        import torch
+        world = dist.get_world_size(group) if multi else 1
+        # rgb * scale; alpha back to the reference's 1 (every rank contributed its own 1): one contiguous pass
+        out *= torch.tensor([scale, scale, scale, 1.0 / world], dtype=out.dtype, device=out.device)
     return out
 
 
