@@ -225,7 +225,7 @@ void build_fast_tree(const float* tris_raw, int nTriangles, const float* nodes_r
 
     std::vector<Node> nodes;
     nodes.reserve(prims.size());
-    Builder b{prims, 0, env_int("PT_LEAF_MAX", 4, 1, 255), 1.0f};
+    Builder b{prims, 0, env_int("PT_LEAF_MAX", 4, 1, 255), 0.01f * (float)env_int("PT_SAH_CNODE_PCT", 100, 1, 10000)};
     Box bounds;
     int64_t root = 0;
     int max_depth = 1, n_leaves = 0;
