@@ -348,9 +348,14 @@ def run_ours(args):
         render_step(frame); frame += spp
         if world > 1:
             if rank == 0:                              # the job's result is the combined image on rank 0
-                with torch.cuda.stream(stream):
-                    host.copy_(combined, non_blocking=True)
-            stream.synchronize()
+                # copied on torch's OWN stream (ordered after the reduce): a pinned tensor remembers the streams that used
+                # it, and the context's stream (an ExternalStream here) is destroyed by pt.close() before torch lets go of it
+                cur = torch.cuda.current_stream()
+                cur.wait_stream(stream)
+                host.copy_(combined, non_blocking=True)
+                cur.synchronize()
+            else:
+                stream.synchronize()
         else:
             pt.readback_into(host.data_ptr(), host.numel() * 4)
     barrier()
@@ -435,8 +440,12 @@ def run_ours(args):
             line["basic_gpu"] = {"value": 256 * 256 * 200 / wall / 1e6, "unit": "Mpaths/s", "seconds": wall, "device_ms": ms,
                                  "sample": "pt_basic_render, 256x256 Cornell box, 200 samples, wall clock incl. the image copy back"}
         print(json.dumps(line), flush=True)
+    # every torch object that touched the context's stream or memory goes before the context does
+    del host, fb, combined, flush
+    torch.cuda.synchronize()
     pt.close()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
