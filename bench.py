@@ -257,6 +257,7 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device — libpt.so has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # stdout carries the one JSON line, not NCCL's version banner
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     # the host BVH build (the reference's SAH builder, all cores) runs once: rank 0 builds and caches, the others load
     if world > 1 and rank != 0:
