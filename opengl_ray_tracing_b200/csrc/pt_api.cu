@@ -64,7 +64,7 @@ struct pt_ctx {
     unsigned* cost = nullptr;    // cost map, allocated by pt_enable_cost_map
     pt::WaveBuffers wf;          // wavefront path state, allocated at the first wavefront render
     void* wf_block = nullptr;
-    uint32_t* sched = nullptr;   // persistent pipeline: work head + per-tile progress
+    uint32_t* sched = nullptr;   // persistent pipeline: work head
     float* sobol_tab = nullptr;  // variant 2: Sobol coordinates of the frames of one launch, [sobol_cap][8]
     size_t sobol_cap = 0;
     uchar4* display = nullptr;   // pt_readback_display staging
@@ -599,10 +599,7 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
         std::memset(&p.wf, 0, sizeof p.wf);
     }
     const bool persistent = c->cfg.pipeline == PT_PIPELINE_PERSISTENT;
-    if (persistent && !c->sched) {
-        const size_t ntiles = (size_t)((c->cfg.width + 7) / 8 + 64) * (size_t)((c->cfg.height + 7) / 8) * 2;   // 8x4 warp tiles (+ per-strip round-up of the diagonal split)
-        CK(cudaMalloc(&c->sched, (64 + ntiles) * sizeof(uint32_t)));
-    }
+    if (persistent && !c->sched) CK(cudaMalloc(&c->sched, 64 * sizeof(uint32_t)));   // the persistent kernel's work head
     p.sched = c->sched;
     {
         // visiting order of the tile rows (render_persistent): 0 = the kernel's own rule, PT_SCHED_STRIDE=1 = bottom to top

@@ -130,7 +130,7 @@ struct RenderParams {
     WaveBuffers wf;             // PT_PIPELINE_WAVEFRONT only
     uint32_t sched_stride;      // PT_PIPELINE_PERSISTENT: tile rows are visited in this many interleaved passes (0: the kernel's rule)
     const float* sobol_tab;     // variant 2: [n_frames][8] Sobol coordinates of this launch's frames (written by sobol_table_kernel) or null
-    uint32_t* sched;            // PT_PIPELINE_PERSISTENT: [0] work head, [64 + tile] next frame allowed to accumulate
+    uint32_t* sched;            // PT_PIPELINE_PERSISTENT: [0] work head (the next frame a pixel accepts travels in the pixel's own .w)
     unsigned* cost;             // optional W*H cost map (SM cycles spent on the pixel by the last launch) or null
 };
 

@@ -25,12 +25,6 @@ static __constant__ uint32_t c_sobol_v[8 * 32] = {
 #include "pt_sobol_v.inc"
 };
 
-#ifndef PT_LIGHT_TAB
-#define PT_LIGHT_TAB 1            // light samples through the per-texel table (below)
-#endif
-#ifndef PT_SBRDF_MERGED
-#define PT_SBRDF_MERGED 1        // SampleBRDF with one toNormalHemisphere site
-#endif
 // ---- arithmetic configurations ------------------------------------------------------------------
 struct MathExact {                // include/ptmath.h: the oracle's definition of the GLSL transcendentals
     static __device__ __forceinline__ float sin(float a) { return pt_sinf(a); }
@@ -49,10 +43,10 @@ struct MathFast {                 // SFU approximations where CUDA has them
     static __device__ __forceinline__ float pow(float a, float b) { return __powf(a, b); }
 };
 struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = false; };
-struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = PT_LIGHT_TAB != 0; };
-struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = PT_LIGHT_TAB != 0; };
-struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = PT_LIGHT_TAB != 0; };
-struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  static const bool LIGHT_TAB = PT_LIGHT_TAB != 0; };
+struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = true; };
+struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true; };
+struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true; };
+struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  static const bool LIGHT_TAB = true; };
 
 // counting configuration: histogram of traversal steps (inner nodes + triangles) per ray, log2 buckets
 __device__ __forceinline__ uint32_t ray_steps(const Counter<false>&) { return 0; }
@@ -433,7 +427,6 @@ __device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 
     float rd = xi_3;
     // One toNormalHemisphere site for the three lobes (a warp on a glossy surface holds lanes of all of them): the branches
     // only produce the local vector; the same operations in the same order per lane as the reference's three functions.
-#if PT_SBRDF_MERGED
     V3 v;
     bool half_vector = true;
     if (rd <= p_diffuse) {                                        // SampleCosineHemisphere
@@ -459,30 +452,6 @@ __device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 
     }
     const V3 w = toNormalHemisphere(v, N);
     return half_vector ? reflect3(-V, w) : w;
-#else
-    if (rd <= p_diffuse) {                                        // SampleCosineHemisphere
-        float r = sqrtf(xi_1);
-        float theta = xi_2 * 2.0f * PT_PI;
-        float x = r * M::cos(theta), y = r * M::sin(theta);
-        float z = sqrtf(1.0f - x * x - y * y);
-        return toNormalHemisphere(mk3(x, y, z), N);
-    }
-    float cos_theta_h;
-    if (p_diffuse < rd && rd <= p_diffuse + p_specular) {         // SampleGTR2
-        cos_theta_h = sqrtf((1.0f - xi_2) / (1.0f + g.a2m1_2 * xi_2));
-    } else if (p_diffuse + p_specular < rd) {                     // SampleGTR1
-        const float a2 = g.alpha1 * g.alpha1;
-        cos_theta_h = sqrtf((1.0f - M::pow(a2, 1.0f - xi_2)) / (1.0f - a2));
-    } else {
-        return mk3(0, 1, 0);                                      // only reachable through NaNs
-    }
-    float phi_h = 2.0f * PT_PI * xi_1;
-    float sin_phi_h = M::sin(phi_h), cos_phi_h = M::cos(phi_h);
-    float sin_theta_h = sqrtf(fmaxf(0.0f, 1.0f - cos_theta_h * cos_theta_h));
-    V3 H = mk3(sin_theta_h * cos_phi_h, sin_theta_h * sin_phi_h, cos_theta_h);
-    H = toNormalHemisphere(H, N);
-    return reflect3(-V, H);
-#endif
 }
 
 // ray generation, P:846-850, in strict arithmetic (primary-hit ids must be bit-exact in every mode).
@@ -718,33 +687,21 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
 // The one-thread-per-pixel kernel above runs the n_frames of a pixel back to back in one thread, so a launch lasts
 // at least as long as its most expensive pixel times n_frames (on is-1M: a mesh tile = 3.6 ms of a 6.1 ms launch,
 // SMs 69 % busy, profiles/r01_megakernel_v2.md).  Here a resident warp repeatedly claims the next (tile, frame)
-// item, computes that one sample for its 32 pixels, and folds it into the framebuffer IN FRAME ORDER: progress[tile]
-// is the next frame allowed to accumulate; a warp that finishes frame f early waits for f-1 (which was claimed
-// before it, hence is running or done: no deadlock).  The running mean therefore sees the same sequence of
-// operations as the reference's ping-pong (P:868-869) and results stay bit-identical.
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// Tagged fold (PT_FOLD_TAGGED, default): the frame a pixel is ready for travels in the .w of the pixel's own float4, so
-// the "flag" and the data are ONE aligned 16-byte word — written by one st.relaxed.gpu.v4 and read by one
-// ld.relaxed.gpu.v4, each a single L2 transaction (the same single-copy property NCCL's LL protocols rest on).  No fence,
-// no release/acquire pair, no warp barrier and no separate progress array: the poll IS the accumulator read.
-// Within a launch w = PT_TAG | (next frame index of the launch); the launch's last frame stores w = 1 (the reference's
-// alpha, P:871); the first frame of a launch waits for nothing (kernel boundary).  A NaN pattern cannot collide with the
-// 1.0f / 0.0f a finished or cleared framebuffer holds.
-#ifndef PT_FOLD_TAGGED
-#define PT_FOLD_TAGGED 1
-#endif
+// item, computes that one sample for its 32 pixels, and folds it into the framebuffer IN FRAME ORDER: a lane that
+// finishes frame f early waits for f-1 of its pixel (which was claimed before it, hence is running or done: no
+// deadlock).  The running mean therefore sees the same sequence of operations as the reference's ping-pong
+// (P:868-869) and results stay bit-identical.
+//
+// The frame a pixel is ready for travels in the .w of the pixel's own float4, so the "flag" and the data are ONE
+// aligned 16-byte word — written by one st.relaxed.gpu.v4 and read by one ld.relaxed.gpu.v4, each a single L2
+// transaction (the same single-copy property NCCL's LL protocols rest on).  No fence, no release/acquire pair, no warp
+// barrier and no separate progress array: the poll IS the accumulator read.  Within a launch w = PT_TAG | (next frame
+// index of the launch); the launch's last frame stores w = 1 (the reference's alpha, P:871); the first frame of a
+// launch waits for nothing (kernel boundary).  A NaN pattern cannot collide with the 1.0f / 0.0f a finished or cleared
+// framebuffer holds.  (Measured against the protocol it replaced — lane 0 ld.acquire on a per-tile progress word,
+// __syncwarp, __ldcg, __stcg, __syncwarp, lane 0 st.release — and against K consecutive frames per item, which
+// PT_ITEM_FRAMES still selects, and an L2 prefetch of the accumulator line: DESIGN.md §5, §9.)
 #define PT_TAG 0xffc00000u
-#ifndef PT_FOLD_PREFETCH
-#define PT_FOLD_PREFETCH 0
-#endif
 #ifndef PT_ITEM_FRAMES
 #define PT_ITEM_FRAMES 1           // consecutive frames of a tile computed by one claim and folded together
 #endif
@@ -770,12 +727,8 @@ __global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) rende
     const int lane = threadIdx.x & 31;
     const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
     const uint32_t ntiles = tm.count();                // owned 8x4 warp tiles
-#if PT_FOLD_TAGGED
     const uint32_t ngroups = (p.n_frames + PT_ITEM_FRAMES - 1u) / PT_ITEM_FRAMES;   // an item = PT_ITEM_FRAMES consecutive frames of one tile
     const uint32_t nitems = ntiles * ngroups;
-#else
-    const uint32_t nitems = ntiles * p.n_frames;
-#endif
     // Order of the tile rows inside a frame: S passes over the rows a, a + S, a + 2S, ... (a = 0 .. S-1) instead of bottom to
     // top.  On the metric scene the lower half of the image is floor (three rays and two BRDF evaluations per sample: issue
     // bound) and the upper half sky (one trivial ray: bound by the framebuffer stream); bottom to top, the resident warps
@@ -785,9 +738,7 @@ __global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) rende
     uint32_t S = p.sched_stride;
     if (S == 0u) S = VARIANT == 2 ? max(1u, (uint32_t)(0.74f * (float)ntiles / (float)(gridDim.x * (PT_PERSIST_THREADS / 32u)) + 0.5f)) : 1u;
     S = min(S, max(1u, (uint32_t)tm.rows));
-    uint32_t* head = p.sched;                          // [0] = next item; progress starts 64 words in
-    uint32_t* progress = p.sched + 64;
-    (void)progress;
+    uint32_t* head = p.sched;                          // [0] = next item
     uint32_t nrays = 0;
     Counter<Cfg::COUNT> cnt;
     for (;;) {
@@ -811,15 +762,11 @@ __global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) rende
             const int px = p.x0 + tx * 8 + (lane & 7);
             const int py = p.y0 + strip * 4 + (lane >> 3);
             const bool valid = px < p.x1 && py < p.y1;
-#if PT_FOLD_TAGGED
             const long long t_start = p.cost ? clock64() : 0;
             const uint32_t fa = f * PT_ITEM_FRAMES;         // first frame (index within the launch) of this item
             const uint32_t nk = min((uint32_t)PT_ITEM_FRAMES, p.n_frames - fa);
             V3 c[PT_ITEM_FRAMES];
             int primary = -1;
-#if PT_FOLD_PREFETCH
-            if (valid) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.accum + (size_t)py * p.width + px));
-#endif
 #pragma unroll 1
             for (uint32_t k2 = 0; k2 < nk; k2++) {
                 const uint32_t frame = p.first_frame + (fa + k2) * p.frame_stride;
@@ -861,39 +808,6 @@ __global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) rende
                 }
                 st_relaxed_v4(slot, ax, ay, az, last ? 0x3f800000u : (PT_TAG | ((fa + nk) & 0x3fffffu)));
             }
-#else
-            const uint32_t frame = p.first_frame + f * p.frame_stride;
-            const long long t_start = p.cost ? clock64() : 0;
-            V3 c = mk3(0, 0, 0);
-            int primary = -1;
-            if (valid) c = shade_sample<Cfg, VARIANT>(p, px, py, frame, p.sobol_tab ? p.sobol_tab + (size_t)f * 8 : nullptr, primary, nrays, cnt);
-            // ordered accumulation
-            if (lane == 0) while (ld_acquire_u32(progress + tile) != f) __nanosleep(32);
-            __syncwarp();
-            if (valid) {
-                const size_t idx = (size_t)py * p.width + px;
-                float4 acc = __ldcg(p.accum + idx);        // L2: another SM wrote the previous frame
-                if (p.accumulate_sum) {
-                    acc.x = s_add(acc.x, c.x); acc.y = s_add(acc.y, c.y); acc.z = s_add(acc.z, c.z);
-                } else {
-                    float a = s_div(1.0f, (float)(frame + 1u));
-                    float b = s_sub(1.0f, a);
-                    acc.x = s_add(s_mul(acc.x, b), s_mul(c.x, a));
-                    acc.y = s_add(s_mul(acc.y, b), s_mul(c.y, a));
-                    acc.z = s_add(s_mul(acc.z, b), s_mul(c.z, a));
-                }
-                acc.w = 1.0f;
-                __stcg(p.accum + idx, acc);
-                if (f + 1 == p.n_frames && p.primary_ids) p.primary_ids[idx] = primary;
-                if (p.cost) {
-                    const unsigned dt = (unsigned)(clock64() - t_start);
-                    p.cost[idx] = f == 0 ? dt : p.cost[idx] + dt;
-                }
-            }
-            // publish: the warp barrier orders every lane's store before lane 0's release store, and release is cumulative
-            __syncwarp();
-            if (lane == 0) st_release_u32(progress + tile, f + 1);
-#endif
         }
     }
     for (int o = 16; o > 0; o >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o);
@@ -906,7 +820,7 @@ cudaError_t launch_persistent(const RenderParams& p, int variant, int num_sms, c
     const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
     const size_t ntiles = tm.count();
     if (ntiles == 0) return cudaSuccess;
-    cudaError_t e = cudaMemsetAsync(p.sched, 0, (64 + ntiles) * sizeof(uint32_t), stream);
+    cudaError_t e = cudaMemsetAsync(p.sched, 0, 64 * sizeof(uint32_t), stream);   // the work head (its own 256 bytes)
     if (e != cudaSuccess) return e;
     if (variant == 2 && p.sobol_tab)
         sobol_table_kernel<<<(p.n_frames * 8 + 255) / 256, 256, 0, stream>>>(const_cast<float*>(p.sobol_tab), p.first_frame, p.n_frames, p.frame_stride);
