@@ -7,8 +7,10 @@
 //   trigeo       48 B / triangle   : p1,p2,p3 + the unit face normal, computed with the exact operations of
 //                                    hitTriangle (P:263) so the precomputation changes no bit
 //   trishade     48 B / triangle   : vertex normals + material id (fetched once per ray, for the winning hit)
-//   materials    64 B / material   : de-duplicated (the reference stores all 72 B per triangle)
+//   materials   128 B / material   : de-duplicated (the reference stores all 72 B per triangle); second half = what the
+//                                    Disney functions derive from the material alone (pt_shade.cuh MaterialD)
 //   hdr4/cache4  16 B / texel      : float4 instead of 12-byte texels that straddle sectors
+//   light_tab    32 B / texel      : variant 2 — what a light sample through each hdrCache texel evaluates to (pt_shade.cuh)
 #include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 
