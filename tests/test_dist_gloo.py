@@ -74,6 +74,7 @@ def test_two_ranks_match_one(tmp_path, split):
         assert got[..., :3].tobytes() == ref[..., :3].tobytes(), "tile split must be bit-identical to one renderer"
     else:
         assert rrmse(got, ref) < 1e-5          # same samples, different fp32 summation order
+        assert (got[..., 3] == 1.0).all(), "the combined image carries the reference's alpha 1, not the sum of the ranks' alphas"
 
 
 def test_plans_partition_the_work():
