@@ -203,6 +203,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        # torchrun exports OMP_NUM_THREADS=1 to its workers; this arm is rank 0 alone on ALL host cores (the OpenMP
+        # runtime reads the variable when the oracle's library is loaded, below)
+        os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     from oracle import pyoracle as O
     sc, W, H, _ = build_workload(args.workload)
     reg = crop_region(W, H)
