@@ -416,6 +416,8 @@ def run_ours(args):
             with open(tpath) as f:
                 tj = json.load(f).get(args.workload, {})
             traffic, issue = tj.get("dram_bytes_per_launch"), tj.get("issue")
+            if world > 1 or spp != 256:
+                traffic = issue = None                 # the committed capture is ONE 256-frame launch of the whole image on one GPU
         line["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                             "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": bytes_per_ray,
                             "inner_per_ray": cs["inner_visits"] / max(1, cs["rays"]), "tris_per_ray": cs["tri_tests"] / max(1, cs["rays"]),
