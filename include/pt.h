@@ -196,6 +196,12 @@ int pt_basic_render(int device, const PtBasicShape* shapes, int n_shapes, int wi
 int pt_basic_imshow(const double* image, int width, int height, unsigned char* rgb8);
 const char* pt_basic_last_error(void);
 
+/* Measurement probe ("L2 peak must be measured on the box"): streams 16-byte ld.global.nc loads from every
+   resident thread over a window of window_mb MiB (<= 64: L2-resident on B200, but beyond the reach of the SMs' L1s because
+   the slice a CTA reads rotates from pass to pass), `passes` times, and reports the best of 5 launches in GB/s.  hbm_gbs
+   (optional): the same kernel over 2 GiB, i.e. the DRAM read rate of the same access pattern.  Needs no context. */
+int pt_measure_l2_read_gbs(int device, int window_mb, int passes, double* gbs, double* hbm_gbs);
+
 const char* pt_last_error(void);
 /* "sm_100a" build tag + whether a CUDA device is visible; never fails (used by the CPU-only symbol test) */
 const char* pt_build_info(void);

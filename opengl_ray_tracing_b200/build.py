@@ -61,7 +61,7 @@ def build_pt(force=False):
     # production TU: approximate division / square root in SHADING (plain operators) — ray generation, ray/box/triangle
     # tests, RNG, texel addressing and accumulation use the _rn intrinsics, which these flags do not touch; no -ftz.
     units = [("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", ["-prec-div=false", "-prec-sqrt=false"]), ("pt_api", []), ("pt_hdrcache", ["-fmad=false"]),
-             ("pt_basic", ["-fmad=false"])]
+             ("pt_basic", ["-fmad=false"]), ("pt_probe", [])]
     objs = []
     for name, extra in units:
         src = os.path.join(CSRC, name + ".cu")

@@ -14,6 +14,7 @@
 #include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -39,10 +40,10 @@ cudaError_t build_light_table_parity(const DevScene& sc, float4* tab, cudaStream
 cudaError_t build_light_table_fast(const DevScene& sc, float4* tab, cudaStream_t stream);     // pt_kernels_fast.cu
 cudaError_t derive_materials_parity(float4* materials, int n, cudaStream_t stream);
 cudaError_t derive_materials_fast(float4* materials, int n, cudaStream_t stream);
-cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
+cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int num_sms, cudaStream_t stream);
 cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
 cudaError_t launch_persistent_parity(const RenderParams& p, int variant, int which, int grid, cudaStream_t stream);
-cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int which, int grid, cudaStream_t stream);
+cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int which, int num_sms, cudaStream_t stream);
 }
 
 static thread_local std::string g_err;
@@ -57,7 +58,11 @@ static int fail(int code, const std::string& msg) { g_err = msg; return code; }
 struct pt_ctx {
     PtConfig cfg;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // device timing of render launches: a ring of event pairs, folded into render_ms lazily (finished pairs) or at a
+    // synchronising call, so that back-to-back pt_render_spp calls never wait for the previous kernel
+    static const int NEV = 32;
+    cudaEvent_t ev0[NEV] = {}, ev1[NEV] = {};
+    int ev_head = 0, ev_tail = 0;            // pairs [ev_tail, ev_head) are pending
     // framebuffer
     float4* accum = nullptr;
     int* primary_ids = nullptr;
@@ -74,6 +79,7 @@ struct pt_ctx {
     // scene
     bool has_scene = false;
     int fast_depth = 0, n_fast_inner = 0;
+    float fast_pad = 0.0f;       // padding of the production tree's boxes = 2^-17 x (largest |coordinate| of the scene)
     double build_ms = 0.0;
     float *tris_raw = nullptr, *nodes_raw = nullptr;
     float4 *wnodes = nullptr, *wnodes_fast = nullptr, *trigeo_fast = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr, *light_tab = nullptr;
@@ -87,7 +93,6 @@ struct pt_ctx {
     // stats
     unsigned long long samples = 0, launches = 0;
     double render_ms = 0.0;
-    bool timing_pending = false;
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -196,6 +201,15 @@ struct MatHash {
     }
 };
 
+cudaError_t create_events(pt_ctx* c) {
+    for (int i = 0; i < pt_ctx::NEV; i++) {
+        cudaError_t e = cudaEventCreate(&c->ev0[i]);
+        if (e == cudaSuccess) e = cudaEventCreate(&c->ev1[i]);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
 void free_scene(pt_ctx* c) {
     cudaFree(c->trigeo_fast); cudaFree(c->trimeta);
     c->trigeo_fast = nullptr; c->trimeta = nullptr;
@@ -230,31 +244,34 @@ int validate_tree(const float* nodes, int nNodes, int nTriangles, std::string& w
     return max_depth;
 }
 
-// One device allocation carved into the wavefront's struct-of-arrays (DESIGN.md "HBM layout").
+// One device allocation carved into the wavefront's struct-of-arrays (DESIGN.md "HBM layout").  Capacity = PT_WF_PATHS_M
+// million path slots (default 64: 32 frames per wave at 1080p, 8 at 4K; 140 B per slot), never less than one frame.
 int alloc_wavefront(pt_ctx* c) {
     if (c->wf_block) return PT_OK;
     const size_t np = (size_t)c->cfg.width * c->cfg.height;
-    const int mb = c->cfg.max_bounce;
-    const size_t nslots = c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS ? 1 + 2 * (size_t)mb : 1 + (size_t)mb;
-    const size_t ctr_bytes = (size_t)2 * (3 * PT_WF_MAX_BOUNCE + 2) * 64 * sizeof(uint32_t);
+    size_t cap = (size_t)64 << 20;
+    if (const char* e = std::getenv("PT_WF_PATHS_M")) { const long v = std::atol(e); if (v > 0) cap = (size_t)v << 20; }
+    if (cap < np) cap = np;
+    cap = (cap / np) * np;                              // whole frames
+    if (cap >= ((size_t)1 << 31)) cap = ((((size_t)1 << 31) - 1) / np) * np;
+    if (cap < np) return fail(PT_EINVAL, "wavefront pipeline: the framebuffer has more than 2^31 pixels");
+    const size_t ctr_bytes = (size_t)(6 * (PT_WF_MAX_BOUNCE + 1) + 1) * 64 * sizeof(uint32_t);
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
-    const size_t o_ro = take(np * 16), o_rd = take(np * 16), o_hist = take(np * 16), o_fr = take(np * 16), o_sh = take(np * 16);
-    const size_t o_hit = take(np * 8), o_seed = take(np * 4), o_nb = take(np * 4), o_terms = take(np * 16 * nslots);
-    const size_t o_q0 = take(np * 4), o_q1 = take(np * 4), o_q2 = take(np * 4), o_qs = take(np * 4), o_qe = take(np * 4);
+    const size_t o_ro = take(cap * 16), o_rd = take(cap * 16), o_sh = take(cap * 16), o_hist = take(cap * 16), o_fr = take(cap * 16);
+    const size_t o_lo = take(cap * 16), o_cs = take(cap * 16), o_hit = take(cap * 8);
+    const size_t o_qr = take(cap * 8), o_qh = take(cap * 4), o_qm0 = take(cap * 4), o_qm1 = take(cap * 4);
     const size_t o_ctr = take(ctr_bytes);
     cudaError_t e = cudaMalloc(&c->wf_block, off);
     if (e != cudaSuccess) { c->wf_block = nullptr; return fail(PT_ECUDA, std::string("wavefront path state: ") + cudaGetErrorString(e)); }
     char* b = (char*)c->wf_block;
     pt::WaveBuffers& w = c->wf;
-    w.ray_o = (float4*)(b + o_ro); w.ray_d = (float4*)(b + o_rd); w.hist = (float4*)(b + o_hist); w.fr = (float4*)(b + o_fr);
-    w.sh_d = (float4*)(b + o_sh); w.hit = (int2*)(b + o_hit); w.seed = (uint32_t*)(b + o_seed); w.nb = (int*)(b + o_nb);
-    w.terms = (float4*)(b + o_terms);
-    w.q_shade[0] = (uint32_t*)(b + o_q0);
-    for (int k = 1; k <= PT_WF_MAX_BOUNCE; k++) w.q_shade[k] = (uint32_t*)(b + ((k & 1) ? o_q1 : o_q2));   // consumed before re-filled
-    w.q_shadow = (uint32_t*)(b + o_qs); w.q_extend = (uint32_t*)(b + o_qe);
+    w.ray_o = (float4*)(b + o_ro); w.ray_d = (float4*)(b + o_rd); w.sh_d = (float4*)(b + o_sh); w.hist = (float4*)(b + o_hist);
+    w.fr = (float4*)(b + o_fr); w.lo = (float4*)(b + o_lo); w.cs = (float4*)(b + o_cs); w.hit = (int2*)(b + o_hit);
+    w.q_ray = (uint32_t*)(b + o_qr); w.q_hit = (uint32_t*)(b + o_qh); w.q_miss[0] = (uint32_t*)(b + o_qm0); w.q_miss[1] = (uint32_t*)(b + o_qm1);
     w.counters = (uint32_t*)(b + o_ctr);
-    w.npaths = np;
+    w.cap = cap;
+    w.npix = (uint32_t)np;
     return PT_OK;
 }
 
@@ -306,7 +323,7 @@ int pt_create(const PtConfig* cfg, pt_ctx** out) {
     size_t npx = (size_t)cfg->width * cfg->height;
     cudaError_t e;
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess ||
+        (e = create_events(c)) != cudaSuccess ||
         (e = cudaMalloc(&c->accum, npx * sizeof(float4))) != cudaSuccess ||
         (e = cudaMalloc(&c->primary_ids, npx * sizeof(int))) != cudaSuccess ||
         (e = cudaMalloc(&c->ray_counter, 48 * sizeof(unsigned long long))) != cudaSuccess ||
@@ -328,8 +345,10 @@ int pt_destroy(pt_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
     cudaFree(c->wf_block); cudaFree(c->sched); cudaFree(c->sobol_tab); cudaFree(c->display); cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
-    if (c->ev0) cudaEventDestroy(c->ev0);
-    if (c->ev1) cudaEventDestroy(c->ev1);
+    for (int i = 0; i < pt_ctx::NEV; i++) {
+        if (c->ev0[i]) cudaEventDestroy(c->ev0[i]);
+        if (c->ev1[i]) cudaEventDestroy(c->ev1[i]);
+    }
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return PT_OK;
@@ -345,7 +364,9 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     int depth = validate_tree(nodes, nNodes, nTriangles, why);
     if (depth < 0) return fail(PT_EFORMAT, "pt_upload_scene: " + why);
     // depth > 256 is accepted: the reference's stack[256] (pass1.fsh:340) only overflows if a RAY defers more than
-    // 256 subtrees at once, which the kernels detect at run time (PT_ERANGE at the next synchronising call).
+    // 256 subtrees at once; the kernels detect an overflow of their own stacks at run time (PT_MODE_PARITY_REF: 256
+    // entries like the reference; the wide/production traversals: PT_STACK = 128 deferred subtrees on trees of depth
+    // < 64) and report PT_ERANGE at the next synchronising call.
 
     // material de-duplication (host hash over the 18 material floats of each triangle)
     std::vector<int> mat_id((size_t)nTriangles);
@@ -429,6 +450,7 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         pt::build_fast_tree(tris, nTriangles, nodes, nNodes, ft, hw > 0 ? (hw > 32 ? 32 : hw) : 1);
         c->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         root_fast = ft.root_ref; fast_depth = ft.depth; nFastInner = (int)(ft.wnodes.size() / 16);
+        c->fast_pad = ft.pad;
         if (nFastInner >= (1 << 24)) { rc = fail(PT_ERANGE, "pt_upload_scene: traversal tree has >= 2^24 inner nodes"); goto done; }
         CKU(cudaMalloc(&c->wnodes_fast, (ft.wnodes.empty() ? 16 : ft.wnodes.size()) * sizeof(float)));
         if (!ft.wnodes.empty())
@@ -551,19 +573,31 @@ int pt_set_tile_interleave(pt_ctx* c, int world, int rank) {
     return PT_OK;
 }
 
-static int collect_timing(pt_ctx* c) {
-    if (!c->timing_pending) return PT_OK;
-    float ms = 0.f;
-    CK(cudaEventSynchronize(c->ev1));
-    CK(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-    c->render_ms += ms;
-    c->timing_pending = false;
+// Folds finished launch timings into render_ms.  wait = false: only pairs that have completed (never blocks);
+// wait = true (synchronising calls: readback, synchronize, get_stats): all of them, and the kernels' error flag is read.
+static int collect_timing(pt_ctx* c, bool wait = true) {
+    while (c->ev_tail != c->ev_head) {
+        const int i = c->ev_tail % pt_ctx::NEV;
+        if (!wait) {
+            const cudaError_t q = cudaEventQuery(c->ev1[i]);
+            if (q == cudaErrorNotReady) break;
+            if (q != cudaSuccess) return fail(PT_ECUDA, std::string("cudaEventQuery: ") + cudaGetErrorString(q));
+        } else {
+            CK(cudaEventSynchronize(c->ev1[i]));
+        }
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, c->ev0[i], c->ev1[i]));
+        c->render_ms += ms;
+        c->ev_tail++;
+    }
+    if (!wait) return PT_OK;
     int flag = 0;
     CK(cudaMemcpy(&flag, c->error_flag, sizeof flag, cudaMemcpyDeviceToHost));
     if (flag) {
         CK(cudaMemset(c->error_flag, 0, sizeof flag));
-        return fail(PT_ERANGE, "render kernel: traversal stack overflow (a ray deferred more than 256 subtrees; "
-                               "the reference's own stack[256], pass1.fsh:340, would have been overrun) - image is invalid");
+        return fail(PT_ERANGE, "render kernel: traversal stack overflow (a ray deferred more subtrees than the traversal stack holds: "
+                               "256 in PT_MODE_PARITY_REF, where the reference's own stack[256], pass1.fsh:340, would have been overrun; "
+                               "128 in the other modes) - image is invalid");
     }
     return PT_OK;
 }
@@ -579,8 +613,16 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
     if (!c->has_scene) return fail(PT_ENOSCENE, "pt_render_spp: no scene uploaded");
     if (n_frames == 0) return PT_OK;
     CK(cudaSetDevice(c->cfg.device));
-    int rc = collect_timing(c);
+    int rc = collect_timing(c, false);
     if (rc != PT_OK) return rc;
+    if (c->ev_head - c->ev_tail >= pt_ctx::NEV) {             // the ring is full: wait for its oldest pair only
+        const int i = c->ev_tail % pt_ctx::NEV;
+        float ms = 0.f;
+        CK(cudaEventSynchronize(c->ev1[i]));
+        CK(cudaEventElapsedTime(&ms, c->ev0[i], c->ev1[i]));
+        c->render_ms += ms;
+        c->ev_tail++;
+    }
     pt::RenderParams p;
     p.sc = c->sc;
     std::memcpy(p.eye, c->eye, 12);
@@ -590,6 +632,13 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
     p.band_world = c->band_world; p.band_rank = c->band_rank; p.band_diag = c->band_diag;
     p.first_frame = first_frame; p.n_frames = n_frames; p.frame_stride = stride; p.accumulate_sum = accumulate;
     p.max_bounce = c->cfg.max_bounce;
+    {
+        // padding = radius 2^-17 covers the rounding of ray points while |eye| <~ 16 radii (error ~ 4 |o| 2^-24); beyond 8 radii
+        // primary rays are traced on the reference topology (pt_shade.cuh trace<>)
+        const float radius = std::ldexp(c->fast_pad, 17);
+        const float far = std::max(std::fabs(c->eye[0]), std::max(std::fabs(c->eye[1]), std::fabs(c->eye[2])));
+        p.eye_far = (!(far <= 8.0f * radius)) ? 1 : 0;
+    }
     p.accum = c->accum; p.primary_ids = c->primary_ids; p.ray_counter = c->ray_counter; p.work_counters = c->ray_counter + 1; p.cost = c->cost;
     const bool fastmode = c->cfg.mode == PT_MODE_FAST || c->cfg.mode == PT_MODE_FAST_COUNT;
     const bool wavefront = c->cfg.pipeline == PT_PIPELINE_WAVEFRONT;
@@ -609,7 +658,7 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
         p.sched_stride = e && *e ? (uint32_t)std::max(0, std::atoi(e)) : 0u;
     }
     p.sobol_tab = nullptr;
-    if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS && !wavefront) {
+    if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS) {
         if (c->sobol_cap < n_frames) {
             CK(cudaStreamSynchronize(c->stream));            // an earlier launch may still read the old table
             cudaFree(c->sobol_tab); c->sobol_tab = nullptr; c->sobol_cap = 0;
@@ -619,12 +668,13 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
         }
         p.sobol_tab = c->sobol_tab;
     }
-    CK(cudaEventRecord(c->ev0, c->stream));
+    const int evi = c->ev_head % pt_ctx::NEV;
+    CK(cudaEventRecord(c->ev0[evi], c->stream));
     cudaError_t e;
     if (wavefront) {
-        const int grid = (c->num_sms > 0 ? c->num_sms : 148) * 8;
-        e = fastmode ? pt::launch_wavefront_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
-                     : pt::launch_wavefront_parity(p, c->cfg.variant, c->cfg.mode, grid, c->stream);
+        const int sms = c->num_sms > 0 ? c->num_sms : 148;
+        e = fastmode ? pt::launch_wavefront_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, sms, c->stream)
+                     : pt::launch_wavefront_parity(p, c->cfg.variant, c->cfg.mode, sms, c->stream);
     } else if (persistent) {
         const int grid = c->num_sms > 0 ? c->num_sms : 148;   // the launcher multiplies by the kernel's CTAs per SM
         e = fastmode ? pt::launch_persistent_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
@@ -634,11 +684,12 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
                      : pt::launch_parity(p, c->cfg.variant, c->cfg.mode, c->stream);
     }
     if (e != cudaSuccess) return fail(PT_ECUDA, std::string("render kernel launch: ") + cudaGetErrorString(e));
-    CK(cudaEventRecord(c->ev1, c->stream));
-    c->timing_pending = true;
+    CK(cudaEventRecord(c->ev1[evi], c->stream));
+    c->ev_head++;
     if (wavefront) {
-        const int mb = c->cfg.max_bounce;
-        c->launches += (unsigned long long)n_frames * (1 + (mb + 1) + mb * (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS ? 2 : 1) + 1);
+        // per wave of F frames: head + max_bounce x (trace + shade) + accumulate (pt_wavefront.cuh)
+        const unsigned long long F = c->wf.cap / c->wf.npix, waves = (n_frames + F - 1) / F;
+        c->launches += waves * (unsigned long long)(2 + 2 * c->cfg.max_bounce) + (p.sobol_tab ? 1 : 0);
     } else {
         c->launches += p.sobol_tab ? 2 : 1;                  // the render kernel (+ the Sobol tabulation)
     }

@@ -91,25 +91,26 @@ struct DevScene {
     unsigned long long* ray_histogram;   // [33] log2 histogram of steps per ray (PT_MODE_FAST_COUNT)
     int* error_flag;            // set to PT_ERR_* by a kernel that had to give up (checked at the next sync)
 };
-#define PT_ERR_STACK 1          // traversal stack overflow (> 256 deferred subtrees; the reference's stack[256], P:340)
+#define PT_ERR_STACK 1          // traversal stack overflow: more deferred subtrees than PT_STACK (pt_trace.cuh: 128; trace_ref keeps the reference's stack[256], P:340)
 
-// Path state of the wavefront pipeline (pt_wavefront.cuh): struct-of-arrays in HBM, indexed by pixel.
+// Path state of the wavefront pipeline (pt_wavefront.cuh): struct-of-arrays in HBM, indexed by
+// slot = (frame within the wave) * npix + py * width + px; `cap` slots.
 #define PT_WF_MAX_BOUNCE 8
 struct WaveBuffers {
-    float4* ray_o;              // xyz = origin of the ray in flight (the hit point it leaves), w = its sampling pdf
-    float4* ray_d;              // xyz = direction, w = N.L of the sample that produced it
-    float4* hist;               // xyz = path throughput before this ray ("history", P:765)
-    float4* fr;                 // xyz = f_r of the sample that produced the ray
-    float4* sh_d;               // xyz = shadow-ray direction (origin = ray_o)
-    int2* hit;                  // x = triangle | inside << 31, y = bits of t
-    uint32_t* seed;             // wang-hash state carried across the stages
-    int* nb;                    // bounces whose term slots are valid when the path ended
-    float4* terms;              // [slot][path]: slot 0 = Le0, then per bounce (light term,) BRDF-ray term
-    uint32_t* q_shade[PT_WF_MAX_BOUNCE + 1];   // q_shade[0] (paths alive after the primary ray) also drives accumulate
-    uint32_t* q_shadow;
-    uint32_t* q_extend;
+    float4* ray_o;              // xyz = origin of the rays in flight (the hit point they leave), w = sampling pdf of the bounce ray
+    float4* ray_d;              // xyz = bounce-ray direction, w = N.L of the sample that produced it
+    float4* sh_d;               // xyz = shadow-ray direction
+    float4* hist;               // xyz = path throughput before the bounce ray ("history", P:765), w = wang-hash state
+    float4* fr;                 // xyz = f_r of the sample that produced the bounce ray, w = PT_WF_FLAG_* bits
+    float4* lo;                 // xyz = Lo so far, w = material id of the primary hit (Le0); once the path ended: its colour, w = 1
+    float4* cs;                 // xyz = the pending light term of this bounce (zeroed by an occluded shadow ray)
+    int2* hit;                  // bounce ray's hit: x = triangle | inside << 31, y = bits of t
+    uint32_t* q_ray;            // [2 cap] rays of the current bounce: slot | PT_WF_SHADOW_BIT
+    uint32_t* q_hit;            // [cap] paths whose bounce ray hit
+    uint32_t* q_miss[2];        // [cap] paths whose bounce ray escaped or never flew; by bounce parity (shade(b) reads b-1 while it appends to b)
     uint32_t* counters;         // queue tails and work-claim heads, one per 256 bytes
-    size_t npaths;              // = width * height
+    size_t cap;                 // path slots
+    uint32_t npix;              // width * height
 };
 
 struct RenderParams {
@@ -132,6 +133,8 @@ struct RenderParams {
     const float* sobol_tab;     // variant 2: [n_frames][8] Sobol coordinates of this launch's frames (written by sobol_table_kernel) or null
     uint32_t* sched;            // PT_PIPELINE_PERSISTENT: [0] work head (the next frame a pixel accepts travels in the pixel's own .w)
     unsigned* cost;             // optional W*H cost map (SM cycles spent on the pixel by the last launch) or null
+    int eye_far;                // the eye is so far outside the scene that float rounding of ray/triangle points (|o| 2^-23) can exceed the
+                                // production tree's box padding (scene radius 2^-17): primary rays then take the reference topology
 };
 
 // Multi-GPU tile split: which 8x4 pixel warp tiles (tx = column, strip = 4-row strip, both counted from the region's

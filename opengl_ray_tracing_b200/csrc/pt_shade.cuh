@@ -57,10 +57,16 @@ __device__ __forceinline__ void note_ray(const Counter<true>& c, uint32_t before
     atomicAdd(hist + (n ? 32 - __clz(n) : 0), 1ull);
 }
 
+// `far_origin`: the ray starts far outside the scene (a primary ray of a distant eye, RenderParams.eye_far).  What
+// hitTriangle accepts is then fuzzy on the scale of |o| 2^-23 — the rounding of P = o + d t — which the fixed padding of
+// the production tree's boxes (scene radius 2^-17, pt_build.cpp) no longer covers, so such rays are traced on the
+// reference topology with the reference's own box test (trace_wide: exact by construction).  Secondary rays start on
+// the scene and never take this path.
 template <class Cfg>
-__device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d, const bool anyhit, Counter<Cfg::COUNT>& cnt) {
+__device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d, const bool anyhit, Counter<Cfg::COUNT>& cnt, const bool far_origin = false) {
     if (Cfg::RAW) return trace_ref(sc, o, d);         // the reference has no any-hit query: closest hit answers both
     if (Cfg::FAST_TREE) {
+        if (far_origin) return trace_wide_fallback(sc, o, d);
         const uint32_t steps0 = ray_steps(cnt);
         TraceResult tr = trace_fast<PT_STACK>(sc, o, d, anyhit, cnt);
         note_ray(cnt, steps0, sc.ray_histogram);
@@ -509,7 +515,7 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
     int phase = PT_PH_PRIMARY;
     primary_id = -1;
     while (true) {
-        const TraceResult tr = trace<Cfg>(sc, o, d, phase == PT_PH_SHADOW, cnt);
+        const TraceResult tr = trace<Cfg>(sc, o, d, phase == PT_PH_SHADOW, cnt, p.eye_far && phase == PT_PH_PRIMARY);
         nrays++;
         if (VARIANT == 2 && Cfg::LIGHT_TAB && tr.tri < 0 && phase == PT_PH_SHADOW) {
             // ---- the shadow ray reached the environment: colour and pdf of its texel come from the light table (P:781-792) ----
@@ -693,8 +699,8 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
 // (P:868-869) and results stay bit-identical.
 //
 // The frame a pixel is ready for travels in the .w of the pixel's own float4, so the "flag" and the data are ONE
-// aligned 16-byte word — written by one st.relaxed.gpu.v4 and read by one ld.relaxed.gpu.v4, each a single L2
-// transaction (the same single-copy property NCCL's LL protocols rest on).  No fence, no release/acquire pair, no warp
+// aligned 16-byte word — written by one st.relaxed.gpu.b128 and read by one ld.relaxed.gpu.b128, each ONE access in the
+// PTX memory model and a single L2 transaction.  No fence, no release/acquire pair, no warp
 // barrier and no separate progress array: the poll IS the accumulator read.  Within a launch w = PT_TAG | (next frame
 // index of the launch); the launch's last frame stores w = 1 (the reference's alpha, P:871); the first frame of a
 // launch waits for nothing (kernel boundary).  A NaN pattern cannot collide with the 1.0f / 0.0f a finished or cleared
@@ -705,6 +711,10 @@ __global__ void __launch_bounds__(256) render_kernel(const __grid_constant__ Ren
 #ifndef PT_ITEM_FRAMES
 #define PT_ITEM_FRAMES 1           // consecutive frames of a tile computed by one claim and folded together
 #endif
+// ONE 128-bit access each: `.b128` (PTX ISA 8.3+) is a single scalar access in the PTX memory model — tag and data are
+// read, and written, as one morally-strong relaxed operation (a `.v4.u32` access is, formally, four scalar accesses in
+// unspecified order, which would allow "new tag, old rgb").  SASS: LDG.E.128.STRONG.GPU / STG.E.128.STRONG.GPU.
+#if defined(PT_FOLD_V4) && PT_FOLD_V4       // the round-1 form (A/B only, tools/build_variant.py): same SASS opcodes, four scalar accesses in the PTX model
 __device__ __forceinline__ uint4 ld_relaxed_v4(const float4* p) {
     uint4 v;
     asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
@@ -714,6 +724,20 @@ __device__ __forceinline__ void st_relaxed_v4(float4* p, float x, float y, float
     asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(__float_as_uint(x)), "r"(__float_as_uint(y)),
                  "r"(__float_as_uint(z)), "r"(w) : "memory");
 }
+#else
+__device__ __forceinline__ uint4 ld_relaxed_v4(const float4* p) {
+    unsigned long long lo, hi;
+    asm volatile("{\n\t.reg .b128 t;\n\tld.relaxed.gpu.global.b128 t, [%2];\n\tmov.b128 {%0, %1}, t;\n\t}" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
+    uint4 v;
+    v.x = (uint32_t)lo; v.y = (uint32_t)(lo >> 32); v.z = (uint32_t)hi; v.w = (uint32_t)(hi >> 32);
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_v4(float4* p, float x, float y, float z, uint32_t w) {
+    const unsigned long long lo = (unsigned long long)__float_as_uint(x) | ((unsigned long long)__float_as_uint(y) << 32);
+    const unsigned long long hi = (unsigned long long)__float_as_uint(z) | ((unsigned long long)w << 32);
+    asm volatile("{\n\t.reg .b128 t;\n\tmov.b128 t, {%1, %2};\n\tst.relaxed.gpu.global.b128 [%0], t;\n\t}" ::"l"(p), "l"(lo), "l"(hi) : "memory");
+}
+#endif
 
 #define PT_PERSIST_CHUNK 1              // (tile, frame) items claimed per atomic
 #ifndef PT_PERSIST_THREADS

@@ -283,6 +283,70 @@ template <> struct Counter<false> {
     __device__ __forceinline__ void texel(uint32_t) {}
 };
 
+// ---- the deferred-subtree stack of trace_fast (the reference's `int stack[256]`, P:340) -----------------------
+// PT_SMEM_STACK = entries per thread kept in SHARED memory, laid out [level][thread] (consecutive lanes hit consecutive
+// banks: conflict-free); deeper entries overflow into a local-memory array, so the total capacity stays PT_STACK.
+// PT_SMEM_STACK = 0 keeps the whole stack in local memory (L1-resident).  PT_STACK_TOS = 1 additionally holds the top
+// entry in a register, which takes the stack load off the pop -> node-address dependency chain.  Measured: DESIGN.md §9.
+#ifndef PT_SMEM_STACK
+#define PT_SMEM_STACK 0
+#endif
+#ifndef PT_STACK_TOS
+#define PT_STACK_TOS 0
+#endif
+#define PT_STACK_STRIDE 256           // threads per CTA of every kernel that traverses (static_assert in pt_shade.cuh)
+template <int STACK>
+struct TravStack {
+    uint32_t local[STACK > PT_SMEM_STACK ? STACK - PT_SMEM_STACK : 1];
+#if PT_SMEM_STACK > 0
+    uint32_t* sm;
+#endif
+#if PT_STACK_TOS
+    uint32_t tos;
+#endif
+    int sp;
+    __device__ __forceinline__ void init(uint32_t* smem_base) {
+        sp = 0;
+#if PT_SMEM_STACK > 0
+        sm = smem_base + threadIdx.x;
+#else
+        (void)smem_base;
+#endif
+    }
+    __device__ __forceinline__ void put(int k, uint32_t v) {
+#if PT_SMEM_STACK > 0
+        if (k < PT_SMEM_STACK) { sm[k * PT_STACK_STRIDE] = v; return; }
+#endif
+        if (STACK > PT_SMEM_STACK) local[k - PT_SMEM_STACK] = v;
+    }
+    __device__ __forceinline__ uint32_t get(int k) const {
+#if PT_SMEM_STACK > 0
+        if (k < PT_SMEM_STACK) return sm[k * PT_STACK_STRIDE];
+#endif
+        return STACK > PT_SMEM_STACK ? local[k - PT_SMEM_STACK] : PT_REF_NONE;
+    }
+    __device__ __forceinline__ bool full() const { return sp >= STACK; }
+    __device__ __forceinline__ bool empty() const { return sp == 0; }
+    __device__ __forceinline__ void clear() { sp = 0; }
+    __device__ __forceinline__ void push(uint32_t v) {
+#if PT_STACK_TOS
+        if (sp > 0) put(sp - 1, tos);
+        tos = v; sp++;
+#else
+        put(sp++, v);
+#endif
+    }
+    __device__ __forceinline__ uint32_t pop() {
+#if PT_STACK_TOS
+        const uint32_t v = tos;
+        if (--sp > 0) tos = get(sp - 1);
+        return v;
+#else
+        return get(--sp);
+#endif
+    }
+};
+
 // `anyhit` is a run-time flag (shadow rays stop at the first accepted triangle): ONE copy of this loop serves every
 // ray of a path.  While-while form (one node-test site, one triangle-test site: the hot loop is ~250 SASS instructions and stays
 // in the instruction cache): descend inner nodes — nearer child first, farther child pushed — until the current
@@ -292,7 +356,7 @@ template <> struct Counter<false> {
 // at the bottom; a node whose children both miss leaves the node loop the same way and pops where the leaves pop.  With
 // `return`s, a `goto` and a second pop loop inside the nested loops the compiler kept a separate path per site and the
 // lanes of a warp reconverged later: same instructions per ray, is-1M +3.6 %, disney-1M +11 % (tools/ab_run.sh).
-// The stack holds refs only: a deferred subtree is culled by the box tests of its own node when it is popped (a deferred
+// The stack (TravStack above: shared memory and/or local memory) holds refs only: a deferred subtree is culled by the box tests of its own node when it is popped (a deferred
 // LEAF by hit_triangle's t < best), not by an entry distance kept beside the ref — half the stack traffic and no pop loop:
 // is-1M +1.3 %, disney-1M +2.7 %.
 template <int STACK, class CNT>
@@ -302,8 +366,14 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
     TraceResult res; res.tri = -1; res.t = PT_INF; res.inside = false;
     float cull = PT_INF;
     bool tie = false;
-    uint32_t stack_ref[STACK];
-    int sp = 0;
+#if PT_SMEM_STACK > 0
+    __shared__ uint32_t s_stack[PT_SMEM_STACK * PT_STACK_STRIDE];
+    uint32_t* const smem_base = s_stack;
+#else
+    uint32_t* const smem_base = nullptr;
+#endif
+    TravStack<STACK> stk;
+    stk.init(smem_base);
     uint32_t ref = sc.root_fast;
     while (true) {
         while (ref_count(ref) == 0) {                 // inner node: both child boxes and refs in one 64-byte record
@@ -316,8 +386,8 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
             const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
             if (g1 && g2) {
                 const bool left_first = e1 <= e2;
-                if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; return res; }
-                stack_ref[sp++] = left_first ? rref : lref;
+                if (stk.full()) { *sc.error_flag = PT_ERR_STACK; return res; }
+                stk.push(left_first ? rref : lref);
                 ref = left_first ? lref : rref;
             } else if (g1 || g2) {
                 ref = g1 ? lref : rref;
@@ -344,13 +414,13 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
                     }
                     if (!anyhit && tt == res.t) { tie = true; continue; }
                     res.t = tt; res.tri = meta.x; res.inside = ins;
-                    if (anyhit) { sp = 0; break; }    // a shadow ray needs no more than this
+                    if (anyhit) { stk.clear(); break; }   // a shadow ray needs no more than this
                     cull = s_mul(tt, PT_CULL_SLACK);
                 }
             }
         }
-        if (sp == 0) break;                           // the ONE pop site (after a leaf, and after a node whose children both missed)
-        ref = stack_ref[--sp];                        // and the one exit: this lane's ray is finished when nothing is deferred
+        if (stk.empty()) break;                       // the ONE pop site (after a leaf, and after a node whose children both missed)
+        ref = stk.pop();                              // and the one exit: this lane's ray is finished when nothing is deferred
     }
     if (!anyhit && tie) res.tri = -2;                 // caller: re-trace on the reference topology
     return res;

@@ -25,7 +25,7 @@ ACC_MEAN, ACC_SUM = 0, 1
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
-           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_last_error",
+           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_measure_l2_read_gbs", "pt_last_error",
            "pt_build_info"]
 
 
@@ -81,6 +81,7 @@ def lib():
         "pt_last_error": (C.c_char_p, []),
         "pt_build_info": (C.c_char_p, []),
         "pt_calculate_hdr_cache": (C.c_int, [C.c_int, C.POINTER(C.c_float), C.c_int, C.c_int, C.POINTER(C.c_float)]),
+        "pt_measure_l2_read_gbs": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -219,6 +220,13 @@ class PathTracer:
 
 def build_info() -> str:
     return lib().pt_build_info().decode()
+
+
+def measure_l2_read_gbs(device=0, window_mb=48, passes=64):
+    """(L2 GB/s, HBM GB/s) of the ld.global.nc read probe (pt_probe.cu): the L2 roofline denominator for node/triangle fetches."""
+    l2, hbm = C.c_double(), C.c_double()
+    _check(lib().pt_measure_l2_read_gbs(device, window_mb, passes, C.byref(l2), C.byref(hbm)), "pt_measure_l2_read_gbs")
+    return l2.value, hbm.value
 
 
 def calculate_hdr_cache(hdr, device=0):

@@ -1,0 +1,162 @@
+"""GPU parity on BASELINE.json's own configurations (VERDICT r01 "next" 1a/1b), through the C ABI.
+
+Each test renders the config's scene at the config's resolution and compares a CROP with the CPU oracle (the oracle
+runs at ~0.4 M samples/s on the box's cores, so the crop keeps it to seconds):
+  config 2  lambert-100k-1080p   variant 0                 ids bit-exact, PARITY_FAST bit-identical, FAST rRMSE <= 1e-3
+  config 3  disney-1M-1080p      variant 1, 5 bounces      same, on a window that holds the mesh's silhouette
+  config 4  is-1M-1080p          variant 2, 2048x1024 HDR  the bench's exact configuration in PT_MODE_FAST; and a 64x36
+                                                           crop at 4096 spp: converged mean within 0.5 % of the oracle
+  config 5  full-10M-4k          variant 0, buildBVH tree  ids bit-exact on a crop at 3840x2160, also rendered as the
+                                                           eight tile-interleaved shares of a world of 8 into one image
+Scenes come from the same builders bench.py uses (scenes.build with the on-disk cache)."""
+import numpy as np
+import pytest
+
+from helpers import oracle_render, rrmse
+
+pytestmark = pytest.mark.gpu
+
+RRMSE_TOL = 1e-3
+MEAN_TOL = 5e-3
+
+
+@pytest.fixture(scope="module")
+def R():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from opengl_ray_tracing_b200 import renderer
+    return renderer
+
+
+def workload(name):
+    import bench
+    sc, W, H, _ = bench.build_workload(name)
+    return sc, W, H
+
+
+def gpu_crop(R, sc, W, H, reg, first, n, mode, pipeline=None, tiles_of_world=0):
+    pt = R.PathTracer(W, H, sc.variant, mode=mode, pipeline=R.PERSISTENT if pipeline is None else pipeline)
+    pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache)
+    pt.set_camera(sc.eye, sc.cam)
+    pt.set_region(*reg)
+    if tiles_of_world:
+        for rank in range(tiles_of_world):                   # the shares of every rank of a tile split, into ONE framebuffer
+            pt.set_tile_interleave(tiles_of_world, rank)
+            pt.render_spp(first, n)
+    else:
+        pt.render_spp(first, n)
+    img, ids, st = pt.readback(), pt.readback_primary_ids(), pt.stats()
+    pt.close()
+    x0, y0, x1, y1 = reg
+    return img[y0:y1, x0:x1], ids[y0:y1, x0:x1], st
+
+
+def oracle_crop(sc, W, H, reg, first, n):
+    ref, ids, _ = oracle_render(sc, W, H, first, n, region=reg)
+    x0, y0, x1, y1 = reg
+    return ref[y0:y1, x0:x1], ids[y0:y1, x0:x1]
+
+
+def check_config(R, name, reg, frames=2, min_hit=0.2, max_hit=1.0):
+    sc, W, H = workload(name)
+    ref, ids_ref = oracle_crop(sc, W, H, reg, 0, frames)
+    hit = float((ids_ref >= 0).mean())
+    assert min_hit <= hit <= max_hit, "crop holds %.2f hit pixels" % hit
+    img, ids, st = gpu_crop(R, sc, W, H, reg, 0, frames, R.MODE_PARITY_FAST)
+    assert (ids == ids_ref).all(), "%s: primary-hit ids differ (PARITY_FAST)" % name
+    assert img.tobytes() == ref.tobytes(), "%s: PARITY_FAST is not bit-identical to the oracle" % name
+    img, ids, st = gpu_crop(R, sc, W, H, reg, 0, frames, R.MODE_FAST)
+    assert (ids == ids_ref).all(), "%s: primary-hit ids differ (FAST)" % name
+    rr = rrmse(img, ref)
+    assert rr <= RRMSE_TOL, "%s: FAST rRMSE %g" % (name, rr)
+    return sc, W, H, st
+
+
+def test_config2_lambert_100k_radiance(R):
+    # 480x270 around the image centre: mesh, floor, and the emissive quad's light on both
+    check_config(R, "lambert-100k-1080p", (720, 405, 1200, 675))
+
+
+def test_config3_disney_1M_five_bounces(R):
+    # the mesh spans x 634..1286, y 275..643 at 1080p (scale 1.75 at (0,-0.4,0), eye z = 4): this 240x136 window holds its
+    # lower-left silhouette, so both mesh paths (up to 5 bounces) and sky pixels are compared
+    sc, W, H, st = check_config(R, "disney-1M-1080p", (600, 240, 840, 376), min_hit=0.1, max_hit=0.9)
+    assert sc.variant == 1 and sc.max_bounce == 5 and sc.nTriangles > 1000000
+
+
+def test_config4_fast_mode_at_the_bench_configuration(R):
+    # bench.py's workload verbatim (1920x1080, 2048x1024 HDR + hdrCache + light table), the reference arm's centre crop
+    import bench
+    sc, W, H, st = check_config(R, "is-1M-1080p", bench.crop_region(1920, 1080))
+    assert sc.hdr.shape == (1024, 2048, 3) and sc.hdrCache is not None
+
+
+def test_config4_converged_mean_4096_spp(R):
+    """Config 4 names 4096 spp: a 64x36 window (bottom of the mesh + the glossy floor under it) rendered to 4096 frames
+    in PT_MODE_FAST against the oracle's 4096 frames — image mean within 0.5 % (IS/shaders/pass1.fsh:868-869)."""
+    sc, W, H = workload("is-1M-1080p")
+    reg, NF = (928, 340, 992, 376), 4096
+    ref, ids_ref = oracle_crop(sc, W, H, reg, 0, NF)
+    img, ids, _ = gpu_crop(R, sc, W, H, reg, 0, NF, R.MODE_FAST)
+    assert (ids == ids_ref).all()
+    a, b = float(img[..., :3].astype(np.float64).mean()), float(ref[..., :3].astype(np.float64).mean())
+    assert abs(a - b) / b <= MEAN_TOL, "converged mean differs by %.3f %%" % (100 * abs(a - b) / b)
+    assert rrmse(img, ref) <= 10 * RRMSE_TOL                  # 4096 running-mean steps of fast-math samples; the bar at fixed spp is the mean
+    assert 0.05 < (ids_ref >= 0).mean() <= 1.0
+
+
+def test_config5_full_10M_4k_ids_and_tile_split(R):
+    """Ten meshes, 10,035,204 triangles, on the tree of the reference's buildBVH (IS/main.cpp:377-428) at 3840x2160:
+    ids bit-exact and PARITY_FAST bit-identical on a 256x144 crop; the same crop rendered as the eight shares of an
+    8-rank tile split (pt_set_tile_interleave) is the same image bit for bit."""
+    sc, W, H = workload("full-10M-4k")
+    assert sc.nTriangles > 10000000 and (W, H) == (3840, 2160)
+    reg = (1792, 900, 2048, 1044)
+    ref, ids_ref = oracle_crop(sc, W, H, reg, 0, 1)
+    assert 0.2 < (ids_ref >= 0).mean()
+    img, ids, _ = gpu_crop(R, sc, W, H, reg, 0, 1, R.MODE_PARITY_FAST)
+    assert (ids == ids_ref).all() and img.tobytes() == ref.tobytes()
+    one, ids1, _ = gpu_crop(R, sc, W, H, reg, 0, 2, R.MODE_FAST)
+    split, ids8, st = gpu_crop(R, sc, W, H, reg, 0, 2, R.MODE_FAST, tiles_of_world=8)
+    assert (ids1 == ids_ref).all() and (ids8 == ids_ref).all()
+    assert split.tobytes() == one.tobytes(), "the 8-way tile split must be bit-identical to one GPU"
+    assert st["samples"] == 2 * 256 * 144
+
+
+def test_far_camera_primary_ids(R):
+    """the production tree's boxes are padded by 2^-17 of the scene radius; an eye hundreds of radii away makes the
+    rounding of ray points larger than that.  Primary rays of a far eye take the reference topology: ids stay bit-exact."""
+    from helpers import small_scene
+    from opengl_ray_tracing_b200 import scene as S
+    sc = small_scene("disney", "10k", hdr_res=(128, 64))
+    eye, cam = S.camera(12.0, 30.0, 150.0)                    # ~150 scene radii
+    sc = type(sc)(sc.name, sc.variant, sc.max_bounce, sc.tris, sc.nodes, sc.hdr, sc.hdrCache, eye, cam)
+    W = H = 8192
+    reg = (4096 - 96, 4096 - 96, 4096 + 96, 4096 + 96)
+    ref, ids_ref = oracle_crop(sc, W, H, reg, 0, 1)
+    assert 0.05 < (ids_ref >= 0).mean() < 0.95
+    for mode in (R.MODE_PARITY_REF, R.MODE_PARITY_FAST, R.MODE_FAST):
+        for pipeline in ((R.MEGAKERNEL,) if mode == R.MODE_PARITY_REF else (R.MEGAKERNEL, R.PERSISTENT)):
+            img, ids, _ = gpu_crop(R, sc, W, H, reg, 0, 1, mode, pipeline=pipeline)
+            assert (ids == ids_ref).all(), "mode %d pipeline %d" % (mode, pipeline)
+            if mode != R.MODE_FAST:
+                assert img.tobytes() == ref.tobytes()
+
+
+def test_ordered_fold_stress_4096_frames(R):
+    """The persistent kernel folds frames in order through a tag in the pixel's own 16-byte word (one ld/st.relaxed.gpu.b128
+    each).  64x64 pixels x 4096 frames in ONE launch keeps dozens of frames of every tile in flight; the result must
+    equal the megakernel's (frames looped in registers) bit for bit."""
+    from helpers import small_scene
+    sc = small_scene("is", "10k", hdr_res=(256, 128))
+    W = H = 64
+    imgs = []
+    for pipeline in (R.MEGAKERNEL, R.PERSISTENT):
+        pt = R.PathTracer(W, H, sc.variant, mode=R.MODE_PARITY_FAST, pipeline=pipeline)
+        pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache)
+        pt.set_camera(sc.eye, sc.cam)
+        pt.render_spp(0, 4096)
+        imgs.append(pt.readback())
+        pt.close()
+    assert np.isfinite(imgs[1]).all() and (imgs[1][..., 3] == 1.0).all()
+    assert imgs[0].tobytes() == imgs[1].tobytes()

@@ -292,6 +292,24 @@ def test_metric_scene_every_pipeline(R):
     pt.close()
 
 
+def test_wavefront_waves_and_lane_refill(R, monkeypatch):
+    """The wavefront pipeline renders F = capacity / pixels frames per wave; with 1 Mi path slots a 512x512 image gets 4
+    frames per wave, so 10 frames are three waves (4, 4, 2): bit-identical to the megakernel, also as two launches."""
+    monkeypatch.setenv("PT_WF_PATHS_M", "1")
+    for kind in ("is", "disney"):
+        sc = small_scene(kind, "10k", hdr_res=(256, 128), camera=(10.0, 25.0, 2.5))
+        W = H = 512
+        ref, ids_ref, st_ref, _ = render(R, sc, W, H, 0, 10, R.MODE_PARITY_FAST, pipeline=R.MEGAKERNEL)
+        img, ids, st, _ = render(R, sc, W, H, 0, 10, R.MODE_PARITY_FAST, pipeline=R.WAVEFRONT)
+        assert img.tobytes() == ref.tobytes() and (ids == ids_ref).all() and st["rays"] == st_ref["rays"]
+        assert st["launches"] >= 3 * (2 + 2 * sc.max_bounce)
+        img, _, _, pt = render(R, sc, W, H, 0, 7, R.MODE_PARITY_FAST, pipeline=R.WAVEFRONT, close=False)
+        img, ids, _, _ = render(R, sc, W, H, 7, 3, R.MODE_PARITY_FAST, pt=pt)
+        assert img.tobytes() == ref.tobytes() and (ids == ids_ref).all()
+        fast, ids_f, _, _ = render(R, sc, W, H, 0, 10, R.MODE_FAST, pipeline=R.WAVEFRONT)
+        assert (ids_f == ids_ref).all() and rrmse(fast, ref) <= RRMSE_TOL
+
+
 def test_counting_build_and_cost_map(R):
     sc = small_scene("is", "10k", hdr_res=(256, 128))
     W, H, NF = 128, 72, 2

@@ -9,15 +9,22 @@ sys.path.insert(0, ROOT)
 from opengl_ray_tracing_b200 import build as B
 
 name, defs = sys.argv[1], sys.argv[2:]
-B.build_pt()
+fast_only = "--fast-only" in defs              # perf A/B in PT_MODE_FAST: reuse the default build's parity object
+defs = [d for d in defs if d != "--fast-only"]
+if "--no-base" not in defs:
+    B.build_pt()
+defs = [d for d in defs if d != "--no-base"]
 vdir = os.path.join(B.BUILD, "variant_" + name)
 os.makedirs(vdir, exist_ok=True)
 objs = []
 for unit, extra in (("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", ["-prec-div=false", "-prec-sqrt=false"])):
+    if fast_only and unit == "pt_kernels_parity":
+        objs.append(os.path.join(B.BUILD, unit + ".o"))
+        continue
     obj = os.path.join(vdir, unit + ".o")
     B._run(["nvcc", *B.ARCH, *B.NVCC_COMMON, *extra, *defs, "-c", os.path.join(B.CSRC, unit + ".cu"), "-o", obj], log=os.path.join(vdir, unit + ".ptxas.log"))
     objs.append(obj)
-objs += [os.path.join(B.BUILD, u + ".o") for u in ("pt_api", "pt_hdrcache", "pt_basic", "pt_build")]
+objs += [os.path.join(B.BUILD, u + ".o") for u in ("pt_api", "pt_hdrcache", "pt_basic", "pt_probe", "pt_build")]
 out = os.path.join(B.HERE, "libpt_%s.so" % name)
 B._run(["nvcc", *B.ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-lgomp", "-o", out])
 print(out)
