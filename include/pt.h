@@ -166,6 +166,30 @@ int pt_stream(pt_ctx* ctx, void** cuda_stream);
 /* Multiplies the framebuffer's rgb by `scale` — the epilogue after a sample-split NCCL sum. */
 int pt_scale_framebuffer(pt_ctx* ctx, float scale);
 
+/* ---- multi-GPU: one context per GPU, scene replicated, the per-GPU framebuffers combined on demand ----------
+   No reference equivalent (one GPU, no readback).  The contexts may live in one process (one thread per GPU, as ptdrive
+   --gpus N does) or in one process per GPU (torchrun).  NCCL is loaded at pt_comm_init with dlopen("libnccl.so.2").
+   pt_comm_get_unique_id: rank 0 obtains the 128-byte rendezvous id (ncclGetUniqueId) and hands it to the other ranks by any
+   means.  pt_comm_init: collective over the `world` contexts; also maps every peer's framebuffer and rank 0's output
+   images into this context's address space (CUDA IPC across processes, peer access inside one) for the fused combine. */
+#define PT_COMM_ID_BYTES 128
+int pt_comm_get_unique_id(void* id, size_t bytes);
+int pt_comm_init(pt_ctx* ctx, int world, int rank, const void* id, size_t bytes);
+int pt_comm_info(pt_ctx* ctx, int* world, int* rank, int* peer_memory);    /* peer_memory = 1: the one-kernel NVLink path is active */
+int pt_comm_destroy(pt_ctx* ctx);
+/* Collective: combines the framebuffers of all ranks into ONE image on rank 0.
+   kind = PT_COMBINE_SUM       sample split: every rank rendered its frames with PT_ACC_SUM; result rgb = sum / total_frames
+   kind = PT_COMBINE_DISJOINT  tile split: every rank rendered its own tiles (pt_set_tile_interleave / band / region) as the
+                               running mean; the sum of disjoint regions is exact (x + 0), i.e. bit-identical to one GPU
+   Alpha = 1 (P:871).  One kernel per GPU: rank r loads slice r of all framebuffers over NVLink, applies the scale (and for
+   rgba8 the pass3 tone map, shaders/pass3.fsh:14-24) and stores into rank 0's image; rank 0 then copies to rgba_host
+   (W*H float4, row 0 = bottom) and/or rgba8_host (W*H RGBA8, row 0 = top) — either may be NULL; other ranks pass NULL.
+   Each rank's own framebuffer is left untouched, so rendering can continue and be combined again.  Synchronises on rank 0
+   when a host buffer is given. */
+#define PT_COMBINE_SUM      0
+#define PT_COMBINE_DISJOINT 1
+int pt_combine(pt_ctx* ctx, int kind, unsigned total_frames, float* rgba_host, unsigned char* rgba8_host);
+
 int pt_synchronize(pt_ctx* ctx);
 int pt_get_stats(pt_ctx* ctx, PtStats* out);
 int pt_reset_stats(pt_ctx* ctx);
@@ -201,6 +225,10 @@ const char* pt_basic_last_error(void);
    the slice a CTA reads rotates from pass to pass), `passes` times, and reports the best of 5 launches in GB/s.  hbm_gbs
    (optional): the same kernel over 2 GiB, i.e. the DRAM read rate of the same access pattern.  Needs no context. */
 int pt_measure_l2_read_gbs(int device, int window_mb, int passes, double* gbs, double* hbm_gbs);
+
+/* sha256 (16 hex digits) over the SASS of the render kernels inside this library, computed at build time.  An ncu capture
+   (profiles/traffic.json) names the hash of the build it was taken from; bench.py quotes the capture only on a match. */
+const char* pt_kernel_sass_hash(void);
 
 const char* pt_last_error(void);
 /* "sm_100a" build tag + whether a CUDA device is visible; never fails (used by the CPU-only symbol test) */

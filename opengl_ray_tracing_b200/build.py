@@ -23,7 +23,7 @@ BUILD = os.path.join(HERE, "build")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 SCENE_SRC = ["pts_scene.cpp", "pts_bvh.cpp", "pts_hdr.cpp", "pts_meshgen.cpp"]
-CUDA_HDRS = ["pt_common.cuh", "pt_trace.cuh", "pt_shade.cuh", "pt_wavefront.cuh", "pt_sobol_v.inc"]
+CUDA_HDRS = ["pt_common.cuh", "pt_trace.cuh", "pt_shade.cuh", "pt_wavefront.cuh", "pt_sobol_v.inc", "pt_internal.h"]
 
 
 def _run(cmd, log=None):
@@ -55,13 +55,40 @@ def build_scene(force=False):
     return out
 
 
+def sass_hash(kernel_objs):
+    """sha256 over the SASS text (cuobjdump -sass: opcodes and operands, without the encoding comments) of the two render-kernel
+    translation units.  profiles/traffic.json is keyed by it: an ncu capture describes exactly one build of the kernels."""
+    import hashlib
+    import re
+    h = hashlib.sha256()
+    for o in kernel_objs:
+        out = subprocess.run(["cuobjdump", "-sass", o], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, check=True).stdout
+        for line in out.splitlines():
+            m = re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(.*?);", line)
+            if m:
+                h.update(m.group(1).encode())
+            elif "Function :" in line:
+                h.update(line.strip().encode())
+    return h.hexdigest()[:16]
+
+
+def _sass_hash_object(kernel_objs, force=False):
+    """Compiles the hash into libpt.so (pt_kernel_sass_hash): the library itself says which kernels it carries."""
+    src, obj = os.path.join(BUILD, "pt_sasshash.cpp"), os.path.join(BUILD, "pt_sasshash.o")
+    if force or _stale(obj, kernel_objs):
+        with open(src, "w") as f:
+            f.write('extern "C" const char* pt_kernel_sass_hash(void) { return "%s"; }\n' % sass_hash(kernel_objs))
+        _run(["g++", "-O1", "-fPIC", "-c", src, "-o", obj])
+    return obj
+
+
 def build_pt(force=False):
     os.makedirs(BUILD, exist_ok=True)
     hdrs = [os.path.join(CSRC, h) for h in CUDA_HDRS] + [os.path.join(ROOT, "include", "pt.h"), os.path.join(ROOT, "include", "ptmath.h")]
     # production TU: approximate division / square root in SHADING (plain operators) — ray generation, ray/box/triangle
     # tests, RNG, texel addressing and accumulation use the _rn intrinsics, which these flags do not touch; no -ftz.
     units = [("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", ["-prec-div=false", "-prec-sqrt=false"]), ("pt_api", []), ("pt_hdrcache", ["-fmad=false"]),
-             ("pt_basic", ["-fmad=false"]), ("pt_probe", [])]
+             ("pt_basic", ["-fmad=false"]), ("pt_probe", []), ("pt_comm", [])]
     objs = []
     for name, extra in units:
         src = os.path.join(CSRC, name + ".cu")
@@ -69,13 +96,14 @@ def build_pt(force=False):
         if force or _stale(obj, [src] + hdrs):
             _run(["nvcc", *ARCH, *NVCC_COMMON, *extra, "-c", src, "-o", obj], log=os.path.join(BUILD, name + ".ptxas.log"))
         objs.append(obj)
+    objs.append(_sass_hash_object(objs[:2], force))
     src, obj = os.path.join(CSRC, "pt_build.cpp"), os.path.join(BUILD, "pt_build.o")
     if force or _stale(obj, [src]):
         _run(["g++", "-std=c++17", "-O3", "-ffp-contract=off", "-fopenmp", "-fPIC", "-Wall", "-Wextra", "-c", src, "-o", obj])
     objs.append(obj)
     out = os.path.join(HERE, "libpt.so")
     if force or _stale(out, objs):
-        _run(["nvcc", *ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-lgomp", "-o", out])
+        _run(["nvcc", *ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-lgomp", "-ldl", "-o", out])
     return out
 
 

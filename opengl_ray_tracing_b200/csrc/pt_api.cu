@@ -14,6 +14,7 @@
 #include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -24,8 +25,7 @@
 #include <unordered_map>
 #include <vector>
 
-#include "../../include/pt.h"
-#include "pt_common.cuh"
+#include "pt_internal.h"
 
 namespace pt {
 cudaError_t launch_parity(const RenderParams& p, int variant, int which, cudaStream_t stream);
@@ -37,63 +37,16 @@ void build_fast_tree(const float* tris_raw, int nTriangles, const float* nodes_r
 cudaError_t hdr_cache_device(const float* d_rgb, int W, int H, float4* d_cache4, float* d_cache3, cudaStream_t st);   // pt_hdrcache.cu
 cudaError_t launch_fast(const RenderParams& p, int variant, bool count, cudaStream_t stream);
 cudaError_t build_light_table_parity(const DevScene& sc, float4* tab, cudaStream_t stream);   // pt_kernels_parity.cu
-cudaError_t build_light_table_fast(const DevScene& sc, float4* tab, cudaStream_t stream);     // pt_kernels_fast.cu
 cudaError_t derive_materials_parity(float4* materials, int n, cudaStream_t stream);
-cudaError_t derive_materials_fast(float4* materials, int n, cudaStream_t stream);
-cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int num_sms, cudaStream_t stream);
+struct WaveStats { unsigned long long waves = 0, retries = 0, frames = 0; };
+cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int num_sms, cudaStream_t stream, WaveStats* ws);
 cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream);
 cudaError_t launch_persistent_parity(const RenderParams& p, int variant, int which, int grid, cudaStream_t stream);
-cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int which, int num_sms, cudaStream_t stream);
+cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int which, int num_sms, cudaStream_t stream, WaveStats* ws);
 }
 
 static thread_local std::string g_err;
-static int fail(int code, const std::string& msg) { g_err = msg; return code; }
-#define CK(call)                                                                                   \
-    do {                                                                                           \
-        cudaError_t e_ = (call);                                                                   \
-        if (e_ != cudaSuccess)                                                                     \
-            return fail(PT_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));             \
-    } while (0)
-
-struct pt_ctx {
-    PtConfig cfg;
-    cudaStream_t stream = nullptr;
-    // device timing of render launches: a ring of event pairs, folded into render_ms lazily (finished pairs) or at a
-    // synchronising call, so that back-to-back pt_render_spp calls never wait for the previous kernel
-    static const int NEV = 32;
-    cudaEvent_t ev0[NEV] = {}, ev1[NEV] = {};
-    int ev_head = 0, ev_tail = 0;            // pairs [ev_tail, ev_head) are pending
-    // framebuffer
-    float4* accum = nullptr;
-    int* primary_ids = nullptr;
-    unsigned long long* ray_counter = nullptr;
-    int* error_flag = nullptr;
-    unsigned* cost = nullptr;    // cost map, allocated by pt_enable_cost_map
-    pt::WaveBuffers wf;          // wavefront path state, allocated at the first wavefront render
-    void* wf_block = nullptr;
-    uint32_t* sched = nullptr;   // persistent pipeline: work head
-    float* sobol_tab = nullptr;  // variant 2: Sobol coordinates of the frames of one launch, [sobol_cap][8]
-    size_t sobol_cap = 0;
-    uchar4* display = nullptr;   // pt_readback_display staging
-    int num_sms = 0;
-    // scene
-    bool has_scene = false;
-    int fast_depth = 0, n_fast_inner = 0;
-    float fast_pad = 0.0f;       // padding of the production tree's boxes = 2^-17 x (largest |coordinate| of the scene)
-    double build_ms = 0.0;
-    float *tris_raw = nullptr, *nodes_raw = nullptr;
-    float4 *wnodes = nullptr, *wnodes_fast = nullptr, *trigeo_fast = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr, *light_tab = nullptr;
-    int2* trimeta = nullptr;
-    pt::DevScene sc;
-    // camera + region
-    float eye[3] = {0, 0, 4};
-    float cam[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 4, 1};
-    int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
-    int band_world = 1, band_rank = 0, band_diag = 0;
-    // stats
-    unsigned long long samples = 0, launches = 0;
-    double render_ms = 0.0;
-};
+int pt_fail(int code, const std::string& msg) { g_err = msg; return code; }
 
 // ------------------------------------------------------------------------------------------------
 // upload kernels
@@ -244,23 +197,28 @@ int validate_tree(const float* nodes, int nNodes, int nTriangles, std::string& w
     return max_depth;
 }
 
-// One device allocation carved into the wavefront's struct-of-arrays (DESIGN.md "HBM layout").  Capacity = PT_WF_PATHS_M
-// million path slots (default 64: 32 frames per wave at 1080p, 8 at 4K; 140 B per slot), never less than one frame.
+// One device allocation carved into the wavefront's struct-of-arrays (DESIGN.md "HBM layout").  PT_WF_PATHS_M million path
+// slots (default 64; 156 B each incl. queue space) + image slots for the finished colours (16 B each): PT_WF_IMAGE_GB (default
+// 16) worth of whole frames, at least one frame and at least as many frames as pcap / pixels.
 int alloc_wavefront(pt_ctx* c) {
     if (c->wf_block) return PT_OK;
     const size_t np = (size_t)c->cfg.width * c->cfg.height;
-    size_t cap = (size_t)64 << 20;
-    if (const char* e = std::getenv("PT_WF_PATHS_M")) { const long v = std::atol(e); if (v > 0) cap = (size_t)v << 20; }
-    if (cap < np) cap = np;
-    cap = (cap / np) * np;                              // whole frames
-    if (cap >= ((size_t)1 << 31)) cap = ((((size_t)1 << 31) - 1) / np) * np;
-    if (cap < np) return fail(PT_EINVAL, "wavefront pipeline: the framebuffer has more than 2^31 pixels");
-    const size_t ctr_bytes = (size_t)(6 * (PT_WF_MAX_BOUNCE + 1) + 1) * 64 * sizeof(uint32_t);
+    size_t pcap = (size_t)64 << 20, img_bytes = (size_t)16 << 30;
+    if (const char* e = std::getenv("PT_WF_PATHS_M")) { const long v = std::atol(e); if (v > 0) pcap = (size_t)v << 20; }
+    if (const char* e = std::getenv("PT_WF_IMAGE_GB")) { const long v = std::atol(e); if (v > 0) img_bytes = (size_t)v << 30; }
+    if (pcap < np) pcap = np;                                     // one frame with every pixel alive always fits
+    if (pcap >= ((size_t)1 << 31)) pcap = ((size_t)1 << 31) - 1;  // bit 31 of a queue entry marks a shadow ray
+    if (pcap < np) return fail(PT_EINVAL, "wavefront pipeline: the framebuffer has more than 2^31 pixels");
+    size_t frames = std::max<size_t>(std::max<size_t>(1, std::min<size_t>(4096, img_bytes / (np * 16))), pcap / np);
+    if (frames * np >= ((size_t)1 << 32)) frames = (((size_t)1 << 32) - 1) / np;   // image slots are 32-bit
+    const size_t icap = frames * np;
+    const size_t ctr_bytes = (size_t)(6 * (PT_WF_MAX_BOUNCE + 1) + 4) * 64 * sizeof(uint32_t);
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
-    const size_t o_ro = take(cap * 16), o_rd = take(cap * 16), o_sh = take(cap * 16), o_hist = take(cap * 16), o_fr = take(cap * 16);
-    const size_t o_lo = take(cap * 16), o_cs = take(cap * 16), o_hit = take(cap * 8);
-    const size_t o_qr = take(cap * 8), o_qh = take(cap * 4), o_qm0 = take(cap * 4), o_qm1 = take(cap * 4);
+    const size_t o_ro = take(pcap * 16), o_rd = take(pcap * 16), o_sh = take(pcap * 16), o_hist = take(pcap * 16), o_fr = take(pcap * 16);
+    const size_t o_lo = take(pcap * 16), o_cs = take(pcap * 16), o_hit = take(pcap * 8), o_pix = take(pcap * 4);
+    const size_t o_img = take(icap * 16);
+    const size_t o_qr = take(pcap * 8), o_res = take(pcap * 16), o_qh = take(pcap * 4), o_qm0 = take(pcap * 4), o_qm1 = take(pcap * 4);
     const size_t o_ctr = take(ctr_bytes);
     cudaError_t e = cudaMalloc(&c->wf_block, off);
     if (e != cudaSuccess) { c->wf_block = nullptr; return fail(PT_ECUDA, std::string("wavefront path state: ") + cudaGetErrorString(e)); }
@@ -268,10 +226,14 @@ int alloc_wavefront(pt_ctx* c) {
     pt::WaveBuffers& w = c->wf;
     w.ray_o = (float4*)(b + o_ro); w.ray_d = (float4*)(b + o_rd); w.sh_d = (float4*)(b + o_sh); w.hist = (float4*)(b + o_hist);
     w.fr = (float4*)(b + o_fr); w.lo = (float4*)(b + o_lo); w.cs = (float4*)(b + o_cs); w.hit = (int2*)(b + o_hit);
-    w.q_ray = (uint32_t*)(b + o_qr); w.q_hit = (uint32_t*)(b + o_qh); w.q_miss[0] = (uint32_t*)(b + o_qm0); w.q_miss[1] = (uint32_t*)(b + o_qm1);
+    w.pix = (uint32_t*)(b + o_pix); w.img = (float4*)(b + o_img);
+    w.q_ray = (uint32_t*)(b + o_qr); w.res = (int2*)(b + o_res); w.q_hit = (uint32_t*)(b + o_qh);
+    w.q_miss[0] = (uint32_t*)(b + o_qm0); w.q_miss[1] = (uint32_t*)(b + o_qm1);
     w.counters = (uint32_t*)(b + o_ctr);
-    w.cap = cap;
+    w.pcap = pcap; w.icap = icap;
     w.npix = (uint32_t)np;
+    w.fill = 0.75f;
+    if (const char* e = std::getenv("PT_WF_FILL_PCT")) { const long v = std::atol(e); if (v > 0) w.fill = 0.01f * (float)v; }
     return PT_OK;
 }
 
@@ -343,6 +305,7 @@ int pt_destroy(pt_ctx* c) {
     if (!c) return PT_OK;
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    pt_comm_release(c);
     free_scene(c);
     cudaFree(c->wf_block); cudaFree(c->sched); cudaFree(c->sobol_tab); cudaFree(c->display); cudaFree(c->cost); cudaFree(c->accum); cudaFree(c->primary_ids); cudaFree(c->ray_counter); cudaFree(c->error_flag);
     for (int i = 0; i < pt_ctx::NEV; i++) {
@@ -467,9 +430,10 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     }
     CKU(cudaMalloc(&c->materials, (size_t)nMaterials * 8 * sizeof(float4)));
     CKU(cudaMemcpyAsync(c->materials, mat_table.data(), (size_t)nMaterials * 32 * sizeof(float), cudaMemcpyHostToDevice, st));
-    // second half of each record: what the Disney functions derive from the material alone, in this context's arithmetic
-    CKU((c->cfg.mode == PT_MODE_FAST || c->cfg.mode == PT_MODE_FAST_COUNT) ? pt::derive_materials_fast(c->materials, nMaterials, st)
-                                                                          : pt::derive_materials_parity(c->materials, nMaterials, st));
+    // second half of each record: what the Disney functions derive from the material alone.  Evaluated in the EXACT arithmetic
+    // (the parity translation unit) for every mode: a^2 - 1 and friends feed the cancellations of the lobe samplers
+    // (pt_shade.cuh SampleBRDF), where an ulp decides which environment texel a mirror-like surface reflects.
+    CKU(pt::derive_materials_parity(c->materials, nMaterials, st));
     // environment
     CKU(cudaMalloc(&d_tmp, ntex * 3 * sizeof(float)));
     CKU(cudaMalloc(&c->hdr4, ntex * sizeof(float4)));
@@ -504,8 +468,8 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         if (c->cfg.variant == PT_VARIANT_DISNEY_IS_MIS && c->cache4 && c->cfg.mode != PT_MODE_PARITY_REF) {
             // light table: what a light sample through each hdrCache texel evaluates to, in this context's arithmetic (pt_shade.cuh)
             CKU(cudaMalloc(&c->light_tab, ntex * 2 * sizeof(float4)));
-            const bool fast = c->cfg.mode == PT_MODE_FAST || c->cfg.mode == PT_MODE_FAST_COUNT;
-            CKU(fast ? pt::build_light_table_fast(s, c->light_tab, st) : pt::build_light_table_parity(s, c->light_tab, st));
+            // ... in the exact arithmetic for every mode (upload-time work: the production kernel only reads the table)
+            CKU(pt::build_light_table_parity(s, c->light_tab, st));
             CKU(cudaStreamSynchronize(st));
             s.light_tab = c->light_tab;
             c->launches += 1;
@@ -671,10 +635,12 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
     const int evi = c->ev_head % pt_ctx::NEV;
     CK(cudaEventRecord(c->ev0[evi], c->stream));
     cudaError_t e;
+    pt::WaveStats wstats;
     if (wavefront) {
         const int sms = c->num_sms > 0 ? c->num_sms : 148;
-        e = fastmode ? pt::launch_wavefront_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, sms, c->stream)
-                     : pt::launch_wavefront_parity(p, c->cfg.variant, c->cfg.mode, sms, c->stream);
+        // (synchronises once per wave: the host sizes each wave from the survivor count of the one before, pt_wavefront.cuh)
+        e = fastmode ? pt::launch_wavefront_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, sms, c->stream, &wstats)
+                     : pt::launch_wavefront_parity(p, c->cfg.variant, c->cfg.mode, sms, c->stream, &wstats);
     } else if (persistent) {
         const int grid = c->num_sms > 0 ? c->num_sms : 148;   // the launcher multiplies by the kernel's CTAs per SM
         e = fastmode ? pt::launch_persistent_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
@@ -687,9 +653,9 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
     CK(cudaEventRecord(c->ev1[evi], c->stream));
     c->ev_head++;
     if (wavefront) {
-        // per wave of F frames: head + max_bounce x (trace + shade) + accumulate (pt_wavefront.cuh)
-        const unsigned long long F = c->wf.cap / c->wf.npix, waves = (n_frames + F - 1) / F;
-        c->launches += waves * (unsigned long long)(2 + 2 * c->cfg.max_bounce) + (p.sobol_tab ? 1 : 0);
+        // per wave: head + max_bounce x (trace + classify + shade) + accumulate; a repeated wave ran its head twice
+        c->launches += wstats.waves * (unsigned long long)(2 + 3 * c->cfg.max_bounce) + wstats.retries + (p.sobol_tab ? 1 : 0);
+        c->wf_waves += wstats.waves; c->wf_retries += wstats.retries;
     } else {
         c->launches += p.sobol_tab ? 2 : 1;                  // the render kernel (+ the Sobol tabulation)
     }

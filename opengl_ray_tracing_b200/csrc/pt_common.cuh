@@ -93,24 +93,29 @@ struct DevScene {
 };
 #define PT_ERR_STACK 1          // traversal stack overflow: more deferred subtrees than PT_STACK (pt_trace.cuh: 128; trace_ref keeps the reference's stack[256], P:340)
 
-// Path state of the wavefront pipeline (pt_wavefront.cuh): struct-of-arrays in HBM, indexed by
-// slot = (frame within the wave) * npix + py * width + px; `cap` slots.
+// Path state of the wavefront pipeline (pt_wavefront.cuh), struct-of-arrays in HBM.
+//   per PATH (compact ids handed out by wf_head to the paths that survive their primary ray; `pcap` of them)
+//   per IMAGE SLOT = (frame within the wave) * npix + py * width + px (`icap` of them): the finished colour of every sample
 #define PT_WF_MAX_BOUNCE 8
 struct WaveBuffers {
-    float4* ray_o;              // xyz = origin of the rays in flight (the hit point they leave), w = sampling pdf of the bounce ray
-    float4* ray_d;              // xyz = bounce-ray direction, w = N.L of the sample that produced it
-    float4* sh_d;               // xyz = shadow-ray direction
-    float4* hist;               // xyz = path throughput before the bounce ray ("history", P:765), w = wang-hash state
-    float4* fr;                 // xyz = f_r of the sample that produced the bounce ray, w = PT_WF_FLAG_* bits
-    float4* lo;                 // xyz = Lo so far, w = material id of the primary hit (Le0); once the path ended: its colour, w = 1
-    float4* cs;                 // xyz = the pending light term of this bounce (zeroed by an occluded shadow ray)
-    int2* hit;                  // bounce ray's hit: x = triangle | inside << 31, y = bits of t
-    uint32_t* q_ray;            // [2 cap] rays of the current bounce: slot | PT_WF_SHADOW_BIT
-    uint32_t* q_hit;            // [cap] paths whose bounce ray hit
-    uint32_t* q_miss[2];        // [cap] paths whose bounce ray escaped or never flew; by bounce parity (shade(b) reads b-1 while it appends to b)
+    float4* ray_o;              // [pcap] xyz = origin of the rays in flight (the hit point they leave), w = sampling pdf of the bounce ray
+    float4* ray_d;              //        xyz = bounce-ray direction, w = N.L of the sample that produced it
+    float4* sh_d;               //        xyz = shadow-ray direction
+    float4* hist;               //        xyz = path throughput before the bounce ray ("history", P:765), w = wang-hash state
+    float4* fr;                 //        xyz = f_r of the sample that produced the bounce ray, w = PT_WF_FLAG_* bits
+    float4* lo;                 //        xyz = Lo so far, w = material id of the primary hit (Le0)
+    float4* cs;                 //        xyz = the pending light term of this bounce (zeroed when its shadow ray is occluded)
+    int2* hit;                  //        bounce ray's hit: x = triangle | inside << 31, y = bits of t
+    uint32_t* pix;              //        image slot of the path
+    float4* img;                // [icap] colour of the sample (rgb, 1) once its path has ended
+    uint32_t* q_ray;            // [2 pcap] rays of the current bounce: path | PT_WF_SHADOW_BIT
+    int2* res;                  // [2 pcap] what wf_trace found for q_ray[i]: x = triangle | inside << 31 (-1: miss), y = bits of t
+    uint32_t* q_hit;            // [pcap] paths whose bounce ray hit
+    uint32_t* q_miss[2];        // [pcap] paths whose bounce ray escaped or never flew; by bounce parity (shade(b) reads b-1 while it appends to b)
     uint32_t* counters;         // queue tails and work-claim heads, one per 256 bytes
-    size_t cap;                 // path slots
+    size_t pcap, icap;
     uint32_t npix;              // width * height
+    float fill;                 // share of pcap the host sizes the next wave for (0.75; PT_WF_FILL_PCT)
 };
 
 struct RenderParams {

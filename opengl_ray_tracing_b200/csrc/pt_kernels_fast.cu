@@ -12,10 +12,8 @@ cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool coun
     if (count) return launch_persistent<CfgFastCount>(p, variant, grid, stream);
     return launch_persistent<CfgFast>(p, variant, grid, stream);
 }
-cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int num_sms, cudaStream_t stream) {
-    if (count) return launch_wavefront<CfgFastCount>(p, variant, num_sms, stream);
-    return launch_wavefront<CfgFast>(p, variant, num_sms, stream);
+cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int num_sms, cudaStream_t stream, WaveStats* ws) {
+    if (count) return launch_wavefront<CfgFastCount>(p, variant, num_sms, stream, ws);
+    return launch_wavefront<CfgFast>(p, variant, num_sms, stream, ws);
 }
-cudaError_t build_light_table_fast(const DevScene& sc, float4* tab, cudaStream_t stream) { return build_light_table<CfgFast>(sc, tab, stream); }
-cudaError_t derive_materials_fast(float4* materials, int n, cudaStream_t stream) { return derive_materials<CfgFast>(materials, n, stream); }
 }  // namespace pt

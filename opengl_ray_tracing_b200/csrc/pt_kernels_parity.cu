@@ -17,9 +17,9 @@ cudaError_t launch_persistent_parity(const RenderParams& p, int variant, int whi
     return launch_persistent<CfgParityFast>(p, variant, grid, stream);
 }
 // the wavefront pipeline under the parity arithmetic: which = 2 (reference topology, wide nodes) or 3 (fast topology)
-cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int which, int num_sms, cudaStream_t stream) {
-    if (which == 2) return launch_wavefront<CfgParityWide>(p, variant, num_sms, stream);
-    return launch_wavefront<CfgParityFast>(p, variant, num_sms, stream);
+cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int which, int num_sms, cudaStream_t stream, WaveStats* ws) {
+    if (which == 2) return launch_wavefront<CfgParityWide>(p, variant, num_sms, stream, ws);
+    return launch_wavefront<CfgParityFast>(p, variant, num_sms, stream, ws);
 }
 cudaError_t build_light_table_parity(const DevScene& sc, float4* tab, cudaStream_t stream) { return build_light_table<CfgParityWide>(sc, tab, stream); }
 cudaError_t derive_materials_parity(float4* materials, int n, cudaStream_t stream) { return derive_materials<CfgParityWide>(materials, n, stream); }

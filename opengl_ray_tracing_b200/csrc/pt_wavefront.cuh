@@ -3,34 +3,36 @@
 //
 // Round-2 design (the round-1 form processed ONE frame per wave with one ray per lane and no refill, and lost 9x to the
 // persistent kernel; profiles/r01_wavefront.md):
-//   * a WAVE is F frames of the whole region at once (F = path capacity / pixels: 32 frames at 1080p with the default
-//     64 M path slots, ~9 GB of the 180 GB), so every launch carries tens of millions of rays and its tail is noise;
+//   * a WAVE is F frames of the whole region at once.  Only the paths that survive their primary ray get a path slot
+//     (compact ids from one atomic counter), so F adapts to the scene: the host reads the survivor count of every wave and
+//     sizes the next one to fill the path capacity (64 M slots by default) — 32 frames per wave where every pixel hits
+//     geometry, hundreds where most of the image is sky.  Every launch then carries tens of millions of rays;
 //   * secondary rays — shadow and bounce rays of one bounce together — go through ONE queue into a TRAVERSAL-ONLY
-//     persistent kernel (wf_trace) that holds nothing but ray state per lane: a lane whose ray is finished takes the next
-//     ray of the warp's chunk of the queue INSIDE the while-while loop (__ballot_sync / __popc ranks, one atomicAdd per
-//     chunk of 256 rays), so the node loop runs with full warps instead of the 7-10 of 32 lanes the megakernel averages
-//     on mesh rays (north star items 1 and 4);
+//     persistent kernel (wf_trace) that holds nothing but ray state per lane: lanes whose ray is finished write its result
+//     and take the next rays of the warp's chunk of the queue INSIDE the while-while loop (__ballot_sync / __popc ranks,
+//     one atomicAdd per chunk of rays), as soon as PT_WF_REFILL_MIN lanes are free, so the node loop keeps running with
+//     full warps instead of the 7-10 of 32 lanes the megakernel averages on mesh rays (north star items 1 and 4);
 //   * primary rays are coherent (8x4 pixel tiles) and need no queue: wf_head generates, traces and shades them like the
 //     persistent kernel does, then parks the path;
-//   * shading runs over COMPACTED queues (wf_shade: paths whose bounce ray hit; then paths whose bounce ray escaped), so
-//     all 32 lanes of a warp run the same ~1.5 k instructions of Disney BRDF code.
+//   * shading runs over COMPACTED queues (wf_classify splits the traced rays into paths that hit / escaped; wf_shade runs
+//     the ~1.5 k instructions of Disney BRDF code with all 32 lanes of a warp on the same branch).
 //
-// One wave, bounce b = 0 .. max_bounce-1 (launches: 2 + 2 max_bounce):
-//   wf_head        ray generation P:846-850 + primary hitBVH; miss -> sampleHdr, path done; hit -> bounce 0 is shaded:
-//                  light sample -> shadow ray + its MIS-weighted term Cs (pending), BRDF sample -> bounce ray, f_r, pdf
-//   wf_trace(b)    every ray of bounce b: shadow rays (any hit; occluded -> Cs := 0) and bounce rays (closest hit ->
-//                  hit record; the path goes to Q_hit or Q_miss)
-//   wf_shade(b+1)  Q_hit: Lo += Cs, emissive term, history (P:833-837), then bounce b+1 as above;
-//                  Q_miss: Lo += Cs, environment term (MIS-weighted in variant 2, P:819-830), path done
-//   wf_accumulate  per pixel, the wave's F colours folded into the framebuffer IN FRAME ORDER (P:868-869)
+// One wave, bounce b = 0 .. max_bounce-1 (launches: 2 + 3 max_bounce):
+//   wf_head         ray generation P:846-850 + primary hitBVH; miss -> sampleHdr, sample done; hit -> bounce 0 is shaded:
+//                   light sample -> shadow ray + its MIS-weighted term Cs (pending), BRDF sample -> bounce ray, f_r, pdf
+//   wf_trace(b)     every ray of bounce b: result (triangle, t) per queue entry; any-hit for shadow rays
+//   wf_classify(b)  occluded shadow ray -> Cs := 0; bounce ray -> hit record + Q_hit, or Q_miss
+//   wf_shade(b+1)   Q_hit: Lo += Cs, emissive term, history (P:833-837), then bounce b+1 as above;
+//                   Q_miss: Lo += Cs, environment term (MIS-weighted in variant 2, P:819-830), sample done
+//   wf_accumulate   per pixel, the wave's F colours folded into the framebuffer IN FRAME ORDER (P:868-869)
 //
 // Exactness: a path's radiance terms are added to its Lo in the reference's order — the light term of bounce b is
 // computed when bounce b is shaded, parked in `cs`, zeroed by an occluded shadow ray (x + 0 is exact; Lo is never -0)
 // and added by whichever stage touches the path next, BEFORE that stage's own term — and the running mean sees the
 // frames in order, so under the parity arithmetic the pipeline is bit-identical to the megakernel and to the oracle.
-//
-// Path state lives in HBM, struct-of-arrays, indexed by slot = (frame within the wave) * W*H + py*W + px.
 #pragma once
+#include <algorithm>
+
 #include "pt_shade.cuh"
 
 namespace pt {
@@ -42,7 +44,10 @@ namespace pt {
 #define PT_WF_REFILL_MIN 4        // wf_trace: idle lanes of a warp before it stops to fetch new rays (all idle: always)
 #endif
 #ifndef PT_WF_TRACE_CTAS
-#define PT_WF_TRACE_CTAS 5        // resident CTAs (256 threads) per SM the traversal kernel is compiled for
+#define PT_WF_TRACE_CTAS 4        // resident CTAs (256 threads) per SM the traversal kernel is compiled for (4: 64 registers)
+#endif
+#ifndef PT_WF_HEAD_CTAS
+#define PT_WF_HEAD_CTAS 4         // same for wf_head / wf_shade (64 registers)
 #endif
 #define PT_WF_SHADOW_BIT 0x80000000u
 #define PT_WF_FLAG_SHADOW 1u      // fr.w: a shadow ray flies for this bounce (cs holds its pending light term)
@@ -51,13 +56,14 @@ namespace pt {
 // queue counters: one per 256 bytes (counters 32 bytes apart share an L2 atomic unit)
 #define PT_WF_CTR_STRIDE 64       // in uint32
 enum { WF_C_RAY_TAIL = 0, WF_C_RAY_HEAD, WF_C_HIT_TAIL, WF_C_HIT_HEAD, WF_C_MISS_TAIL, WF_C_MISS_HEAD, WF_C_KINDS };
-#define PT_WF_NUM_CTRS (WF_C_KINDS * (PT_WF_MAX_BOUNCE + 1) + 1)      // + the head kernel's item counter
+#define PT_WF_NUM_CTRS (WF_C_KINDS * (PT_WF_MAX_BOUNCE + 1) + 4)      // + the head kernel's item counter, path allocator, overflow flag, wave ray count
 __device__ __forceinline__ uint32_t* wf_ctr(const WaveBuffers& wf, int kind, int b) {
     return wf.counters + (size_t)(kind * (PT_WF_MAX_BOUNCE + 1) + b) * PT_WF_CTR_STRIDE;
 }
-__device__ __forceinline__ uint32_t* wf_item_ctr(const WaveBuffers& wf) {
-    return wf.counters + (size_t)(WF_C_KINDS * (PT_WF_MAX_BOUNCE + 1)) * PT_WF_CTR_STRIDE;
+__host__ __device__ __forceinline__ uint32_t* wf_misc_ctr(const WaveBuffers& wf, int k) {      // 0 item head, 1 paths allocated, 2 overflow, 3 rays of wf_head
+    return wf.counters + (size_t)(WF_C_KINDS * (PT_WF_MAX_BOUNCE + 1) + k) * PT_WF_CTR_STRIDE;
 }
+__device__ __forceinline__ uint32_t* wf_item_ctr(const WaveBuffers& wf) { return wf_misc_ctr(wf, 0); }
 
 // warp-aggregated append: all 32 lanes call this; lanes with pred write id
 __device__ __forceinline__ void wf_push(uint32_t* queue, uint32_t* tail, bool pred, uint32_t id) {
@@ -101,18 +107,19 @@ __device__ __forceinline__ V3 xyz(float4 v) { return mk3(v.x, v.y, v.z); }
 
 // the path is finished: colour = Le0 + Lo (P:862-864; Le0 = emissive of the PRIMARY hit's material, whose id rides in lo.w)
 template <class Cfg>
-__device__ __forceinline__ void wf_finish(const RenderParams& p, uint32_t slot, V3 Lo, int mat0) {
+__device__ __forceinline__ void wf_finish(const RenderParams& p, uint32_t islot, V3 Lo, int mat0) {
     typename MatOf<Cfg::RAW>::T m0;
     load_material<Cfg::RAW>(p.sc, mat0, m0);
-    p.wf.lo[slot] = f4(m0.emissive + Lo, 1.0f);
+    p.wf.img[islot] = f4(m0.emissive + Lo, 1.0f);
 }
 
 // ---- bounce `b` of a path at a closest hit: the body of shade_sample()'s "closest hit" branch ------------------------
 // In: the ray (o, d) that hit, its TraceResult, the path's history / Lo BEFORE this hit and, for b > 0, the f_r, cosw, pdf of
-// the ray.  Parks the path (state arrays) and reports which rays fly next; finishes the path when none does.
+// the ray.  Parks the path (state arrays, index `slot` = path id) and reports which rays fly next; finishes the sample
+// (image slot `islot`) when none does.
 struct WfNext { bool shadow, extend, to_miss; };
 template <class Cfg, int VARIANT>
-__device__ __forceinline__ WfNext wf_shade_hit(const RenderParams& p, uint32_t slot, int px, int py, uint32_t frame, const float* __restrict__ sobol_row,
+__device__ __forceinline__ WfNext wf_shade_hit(const RenderParams& p, uint32_t slot, uint32_t islot, int px, int py, uint32_t frame, const float* __restrict__ sobol_row,
                                                int b, V3 o, V3 d, const TraceResult& tr, V3 history, V3 Lo, V3 f_r, float cosw, float pdf,
                                                uint32_t seed, int mat0, Counter<Cfg::COUNT>& cnt) {
     typedef typename Cfg::M M;
@@ -132,7 +139,7 @@ __device__ __forceinline__ WfNext wf_shade_hit(const RenderParams& p, uint32_t s
         Lo = Lo + history * mat.emissive * f_r * cosw / pdf;                                      // P:833-834
         history = history * (f_r * cosw / pdf);                                                   // P:837
     }
-    if (b >= p.max_bounce) { wf_finish<Cfg>(p, slot, Lo, mat0); return nx; }
+    if (b >= p.max_bounce) { wf_finish<Cfg>(p, islot, Lo, mat0); return nx; }
     const V3 V = -hit.viewDir, N = hit.normal;
     o = hit.hitPoint;
     V3 L;
@@ -192,7 +199,7 @@ __device__ __forceinline__ WfNext wf_shade_hit(const RenderParams& p, uint32_t s
         const float z = rnd(seed);
         const float r = fmaxf(0.0f, sqrtf(1.0f - z * z));
         const float phi = 2.0f * PT_PI * rnd(seed);
-        L = toNormalHemisphere(mk3(r * M::cos(phi), r * M::sin(phi), z), N);
+        L = toNormalHemisphere(mk3(r * M::cos_dir(phi), r * M::sin_dir(phi), z), N);
         pdf = 1.0f / (2.0f * PT_PI);
         cosw = fmaxf(0.0f, dot(L, N));
         if (VARIANT == 1) {
@@ -203,7 +210,7 @@ __device__ __forceinline__ WfNext wf_shade_hit(const RenderParams& p, uint32_t s
             f_r = mat.baseColor / PT_PI;
         }
     }
-    if (!want_shadow && !next_ok) { wf_finish<Cfg>(p, slot, Lo, mat0); return nx; }
+    if (!want_shadow && !next_ok) { wf_finish<Cfg>(p, islot, Lo, mat0); return nx; }
     wf.lo[slot] = f4(Lo, __int_as_float(mat0));
     wf.fr[slot] = f4(f_r, __uint_as_float((want_shadow ? PT_WF_FLAG_SHADOW : 0u) | (next_ok ? PT_WF_FLAG_EXTEND : 0u)));
     wf.ray_o[slot] = f4(o, pdf);                                   // origin of both the shadow ray and the bounce ray
@@ -216,9 +223,11 @@ __device__ __forceinline__ WfNext wf_shade_hit(const RenderParams& p, uint32_t s
 }
 
 // ---- head: generate + primary ray + bounce 0 ----------------------------------------------------------------------
-// work item = (8x4 pixel tile, frame of the wave), claimed dynamically like the persistent kernel's items
+// work item = (8x4 pixel tile, frame of the wave), claimed dynamically like the persistent kernel's items.  Paths that hit
+// get a path id from one warp-aggregated atomic; running out of ids sets the overflow flag (the host repeats the wave
+// with fewer frames).
 template <class Cfg, int VARIANT>
-__global__ void __launch_bounds__(256) wf_head(const __grid_constant__ RenderParams p, uint32_t f0, uint32_t nf) {
+__global__ void __launch_bounds__(256, PT_WF_HEAD_CTAS) wf_head(const __grid_constant__ RenderParams p, uint32_t f0, uint32_t nf) {
     const WaveBuffers& wf = p.wf;
     const int lane = threadIdx.x & 31;
     const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
@@ -237,71 +246,59 @@ __global__ void __launch_bounds__(256) wf_head(const __grid_constant__ RenderPar
         const bool valid = px < p.x1 && py < p.y1;
         const uint32_t frame = p.first_frame + (f0 + fl) * p.frame_stride;
         const size_t idx = (size_t)py * p.width + px;
-        const uint32_t slot = fl * wf.npix + (uint32_t)idx;
-        WfNext nx; nx.shadow = nx.extend = nx.to_miss = false;
+        const uint32_t islot = fl * wf.npix + (uint32_t)idx;
+        uint32_t seed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + frame * 26699u) | 1u;             // P:73-76
+        V3 o = mk3(0, 0, 0), d = mk3(0, 0, 1);
+        TraceResult tr; tr.tri = -1; tr.t = PT_INF; tr.inside = false;
         if (valid) {
-            uint32_t seed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + frame * 26699u) | 1u;         // P:73-76
-            V3 o, d;
             generate_ray(p, px, py, seed, o, d);
-            const TraceResult tr = trace<Cfg>(p.sc, o, d, false, cnt, p.eye_far != 0);
+            tr = trace<Cfg>(p.sc, o, d, false, cnt, p.eye_far != 0);
             nrays++;
             if (f0 + fl + 1u == p.n_frames && p.primary_ids) p.primary_ids[idx] = tr.tri;
             if (tr.tri < 0) {
                 cnt.texel(1u);
-                wf.lo[slot] = f4(sampleHdr<typename Cfg::M>(p.sc, d), 1.0f);                             // P:857-859
-            } else {
-                nx = wf_shade_hit<Cfg, VARIANT>(p, slot, px, py, frame, p.sobol_tab ? p.sobol_tab + (size_t)(f0 + fl) * 8 : nullptr, 0, o, d, tr,
-                                                mk3(1, 1, 1), mk3(0, 0, 0), mk3(0, 0, 0), 0.0f, 1.0f, seed, 0, cnt);
+                wf.img[islot] = f4(sampleHdr<typename Cfg::M>(p.sc, d), 1.0f);                           // P:857-859
             }
+        }
+        // path ids for the lanes whose primary ray hit
+        bool alive = valid && tr.tri >= 0;
+        const uint32_t am = __ballot_sync(0xffffffffu, alive);
+        uint32_t slot = 0;
+        if (am) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(wf_misc_ctr(wf, 1), (uint32_t)__popc(am));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            slot = base + (uint32_t)__popc(am & ((1u << lane) - 1u));
+            if (alive && slot >= wf.pcap) {                                  // out of path slots: this wave is repeated with fewer frames
+                *wf_misc_ctr(wf, 2) = 1u;
+                alive = false;
+            }
+        }
+        WfNext nx; nx.shadow = nx.extend = nx.to_miss = false;
+        if (alive) {
+            wf.pix[slot] = islot;
+            nx = wf_shade_hit<Cfg, VARIANT>(p, slot, islot, px, py, frame, p.sobol_tab ? p.sobol_tab + (size_t)(f0 + fl) * 8 : nullptr, 0, o, d, tr,
+                                            mk3(1, 1, 1), mk3(0, 0, 0), mk3(0, 0, 0), 0.0f, 1.0f, seed, 0, cnt);
         }
         wf_push2(wf.q_ray, wf_ctr(wf, WF_C_RAY_TAIL, 0), nx.shadow, slot | PT_WF_SHADOW_BIT, nx.extend, slot);
         if (VARIANT == 2) wf_push(wf.q_miss[0], wf_ctr(wf, WF_C_MISS_TAIL, 0), nx.to_miss, slot);
     }
-    wf_flush_rays(nrays, p.ray_counter);
+    // primary rays of this wave: added to the context's ray counter by wf_accumulate, i.e. only once the wave is accepted
+    for (int o2 = 16; o2 > 0; o2 >>= 1) nrays += __shfl_xor_sync(0xffffffffu, nrays, o2);
+    if (lane == 0 && nrays) atomicAdd(wf_misc_ctr(wf, 3), nrays);
     flush_counts(cnt, p.work_counters);
 }
 
 // ---- trace: the rays of bounce b -----------------------------------------------------------------------------------
-// Per-warp staging of finished paths (shared memory): results leave for Q_hit / Q_miss 32 at a time, one atomic per
-// 32 entries instead of one per finishing event.
-struct WfStage {
-    uint32_t* buf;       // this warp's 64 entries
-    uint32_t n;          // warp-uniform fill
-};
-__device__ __forceinline__ void wf_stage_add(WfStage& s, bool pred, uint32_t id, uint32_t* queue, uint32_t* tail) {
-    const uint32_t m = __ballot_sync(0xffffffffu, pred);
-    if (m == 0) return;
-    const int lane = threadIdx.x & 31;
-    if (pred) s.buf[s.n + __popc(m & ((1u << lane) - 1u))] = id;
-    s.n += __popc(m);
-    __syncwarp();
-    if (s.n >= 32u) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(tail, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        queue[base + lane] = s.buf[lane];
-        const uint32_t rest = s.n - 32u;
-        const uint32_t carry = (uint32_t)lane < rest ? s.buf[32 + lane] : 0u;
-        __syncwarp();
-        if ((uint32_t)lane < rest) s.buf[lane] = carry;
-        s.n = rest;
-        __syncwarp();
-    }
-}
-__device__ __forceinline__ void wf_stage_flush(WfStage& s, uint32_t* queue, uint32_t* tail) {
-    if (s.n == 0) return;
-    const int lane = threadIdx.x & 31;
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(tail, s.n);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if ((uint32_t)lane < s.n) queue[base + lane] = s.buf[lane];
-    s.n = 0;
+// Output: res[i] for queue entry i — nothing else leaves this kernel (wf_classify turns results into queues), so a finished
+// ray costs its lane one 8-byte store.
+__device__ __forceinline__ int2 wf_pack_result(const TraceResult& r) {
+    return make_int2(r.tri >= 0 ? (r.tri | (r.inside ? (int)0x80000000 : 0)) : -1, __float_as_int(r.t));
 }
 
 // Reference-topology configurations (PT_MODE_PARITY_WIDE): one ray per lane per round, no refill (a correctness mode).
 template <class Cfg>
-__device__ __forceinline__ void wf_trace_simple(const RenderParams& p, int b, uint32_t count, WfStage& sh, WfStage& sm, uint32_t& nrays,
-                                                Counter<Cfg::COUNT>& cnt) {
+__device__ __forceinline__ void wf_trace_simple(const RenderParams& p, int b, uint32_t count, uint32_t& nrays, Counter<Cfg::COUNT>& cnt) {
     const WaveBuffers& wf = p.wf;
     const int lane = threadIdx.x & 31;
     for (;;) {
@@ -310,46 +307,39 @@ __device__ __forceinline__ void wf_trace_simple(const RenderParams& p, int b, ui
 #pragma unroll 1
         for (uint32_t k = 0; k < PT_WF_CHUNK; k += 32) {
             const uint32_t i = base + k + lane;
-            bool hit = false, miss = false;
-            uint32_t slot = 0;
-            if (i < count) {
-                const uint32_t e = wf.q_ray[i];
-                slot = e & ~PT_WF_SHADOW_BIT;
-                const bool shadow = (e & PT_WF_SHADOW_BIT) != 0;
-                const V3 o = xyz(wf.ray_o[slot]), d = xyz(shadow ? wf.sh_d[slot] : wf.ray_d[slot]);
-                const TraceResult tr = trace<Cfg>(p.sc, o, d, shadow, cnt);
-                nrays++;
-                if (shadow) {
-                    if (tr.tri >= 0) wf.cs[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
-                } else if (tr.tri >= 0) {
-                    wf.hit[slot] = make_int2(tr.tri | (tr.inside ? (int)0x80000000 : 0), __float_as_int(tr.t));
-                    hit = true;
-                } else {
-                    miss = true;
-                }
-            }
-            wf_stage_add(sh, hit, slot, wf.q_hit, wf_ctr(wf, WF_C_HIT_TAIL, b));
-            wf_stage_add(sm, miss, slot, wf.q_miss[b & 1], wf_ctr(wf, WF_C_MISS_TAIL, b));
+            if (i >= count) continue;
+            const uint32_t e = wf.q_ray[i], slot = e & ~PT_WF_SHADOW_BIT;
+            const bool shadow = (e & PT_WF_SHADOW_BIT) != 0;
+            const V3 o = xyz(wf.ray_o[slot]), d = xyz(shadow ? wf.sh_d[slot] : wf.ray_d[slot]);
+            const TraceResult tr = trace<Cfg>(p.sc, o, d, shadow, cnt);
+            nrays++;
+            wf.res[i] = wf_pack_result(tr);
         }
     }
 }
 
-// Production topology: trace_fast's while-while loop (pt_trace.cuh — same tests, same order, same results per ray) with the
-// ray state per LANE and a refill point at the top of every round: lanes whose ray is finished take the next rays of the
-// warp's chunk of the queue.  A lane without a ray carries ref = PT_REF_NONE through both loops.
+// Production topology: trace_fast's while-while loop (pt_trace.cuh — same tests, same order, same result per ray) with the
+// ray state per LANE.  At the top of every round the warp counts its free lanes (no ray, or ray finished); once there are
+// PT_WF_REFILL_MIN of them (or none is busy) the finished ones store their results and all free lanes take the next rays
+// of the warp's chunk of the queue, together — one pass through the ~70 instructions of result store + ray set-up per
+// PT_WF_REFILL_MIN rays instead of one per ray.  A lane without work carries ref = PT_REF_NONE through both loops.
 template <class Cfg>
-__device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, uint32_t count, WfStage& sh, WfStage& sm, uint32_t* smem_stack,
-                                                uint32_t& nrays, Counter<Cfg::COUNT>& cnt) {
+__device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, uint32_t count, uint32_t* smem_stack, uint32_t& nrays,
+                                                Counter<Cfg::COUNT>& cnt) {
     const WaveBuffers& wf = p.wf;
     const DevScene& sc = p.sc;
     const int lane = threadIdx.x & 31;
     const uint32_t lt = (1u << lane) - 1u;
     uint32_t* const head = wf_ctr(wf, WF_C_RAY_HEAD, b);
+    // chunk = rays a warp claims per atomic: PT_WF_CHUNK for long queues, less (>= 32) when the queue holds fewer than ~4
+    // chunks per resident warp, so that a short queue (late bounces) still spreads over every SM
+    const uint32_t chunk = max(32u, min((uint32_t)PT_WF_CHUNK, (count / (gridDim.x * 8u * 4u)) & ~31u));
     uint32_t chunk_next = 0, chunk_end = 0;            // warp-uniform: the part of the queue this warp still owns
     bool more = true;                                  // the queue may hold unclaimed chunks
-    // per-lane ray
-    bool have = false;
-    uint32_t entry = 0;
+    // per-lane ray: state 0 = none, 1 = in flight, 2 = finished (result not stored yet)
+    int state = 0;
+    uint32_t qi = 0;                                   // its queue position
+    bool anyhit = false;
     Ray r;
     r.o = r.d = r.inv = mk3(0, 0, 0);
     CullRay cr;
@@ -362,44 +352,52 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
     stk.init(smem_stack);
     uint32_t ref = PT_REF_NONE;
     for (;;) {
-        // ---- refill ----
+        // ---- store finished results, refill ----
         {
-            uint32_t idle = __ballot_sync(0xffffffffu, !have);
+            const uint32_t busy = __ballot_sync(0xffffffffu, state == 1);
+            const uint32_t nfree = 32u - (uint32_t)__popc(busy);
             const bool can_fetch = more || chunk_next < chunk_end;
-            if (idle == 0xffffffffu || (can_fetch && (uint32_t)__popc(idle) >= (uint32_t)PT_WF_REFILL_MIN)) {
-                for (;;) {
+            if (busy == 0u || (nfree >= (uint32_t)PT_WF_REFILL_MIN && can_fetch)) {      // (queue exhausted: results wait for the warp's last ray)
+                if (state == 2) {
+                    if (Cfg::COUNT) atomicAdd(sc.ray_histogram + (steps ? 32 - __clz(steps) : 0), 1ull);
+                    if (!anyhit && tie) { cnt.tie(); res = trace_wide_fallback(sc, r.o, r.d); }   // exact tie: let the reference order decide
+                    wf.res[qi] = wf_pack_result(res);
+                    state = 0;
+                }
+                uint32_t idle = ~busy;                 // every lane that is not in flight is free now
+                while (can_fetch) {
                     if (chunk_next >= chunk_end) {
                         if (!more) break;
-                        const uint32_t base = wf_claim(head, (uint32_t)PT_WF_CHUNK);
+                        const uint32_t base = wf_claim(head, chunk);
                         if (base >= count) { more = false; break; }
                         chunk_next = base;
-                        chunk_end = min(base + (uint32_t)PT_WF_CHUNK, count);
+                        chunk_end = min(base + chunk, count);
                     }
                     const uint32_t n_idle = (uint32_t)__popc(idle);
                     const uint32_t take = min(n_idle, chunk_end - chunk_next);
                     const uint32_t rank = (uint32_t)__popc(idle & lt);
-                    if (!have && rank < take) {
-                        entry = wf.q_ray[chunk_next + rank];
-                        const uint32_t slot = entry & ~PT_WF_SHADOW_BIT;
+                    if (state == 0 && rank < take) {
+                        qi = chunk_next + rank;
+                        const uint32_t entry = wf.q_ray[qi], slot = entry & ~PT_WF_SHADOW_BIT;
+                        anyhit = (entry & PT_WF_SHADOW_BIT) != 0;
                         const float4 o4 = wf.ray_o[slot];
-                        const float4 d4 = (entry & PT_WF_SHADOW_BIT) ? wf.sh_d[slot] : wf.ray_d[slot];
+                        const float4 d4 = anyhit ? wf.sh_d[slot] : wf.ray_d[slot];
                         r.o = xyz(o4); r.d = xyz(d4);
                         cr = make_cull_ray(r.o, mk3(rcp_approx(r.d.x), rcp_approx(r.d.y), rcp_approx(r.d.z)));
                         res.tri = -1; res.t = PT_INF; res.inside = false;
                         cull = PT_INF; tie = false; steps = 0;
                         stk.clear();
                         ref = sc.root_fast;
-                        have = true;
+                        state = 1;
                         nrays++;
                     }
                     chunk_next += take;
                     if (take == n_idle) break;
-                    idle = __ballot_sync(0xffffffffu, !have);
+                    idle = __ballot_sync(0xffffffffu, state == 0);
                 }
-                if (__ballot_sync(0xffffffffu, have) == 0u) break;      // every lane idle and nothing left to fetch
+                if (__ballot_sync(0xffffffffu, state == 1) == 0u) break;      // nothing in flight and nothing left to fetch
             }
         }
-        const bool anyhit = (entry & PT_WF_SHADOW_BIT) != 0;
         // ---- one round of trace_fast: descend to a leaf, test it, pop ----
         while (ref_count(ref) == 0) {
             const float4* w = sc.wnodes_fast + 4 * (size_t)ref;
@@ -446,30 +444,10 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
                 }
             }
         }
-        // ---- pop, or finish this lane's ray ----
-        bool fin = false;
-        if (have) {
-            if (stk.empty()) { fin = true; ref = PT_REF_NONE; }
+        // ---- pop, or this lane's ray is finished ----
+        if (state == 1) {
+            if (stk.empty()) { state = 2; ref = PT_REF_NONE; }
             else ref = stk.pop();
-        }
-        if (__ballot_sync(0xffffffffu, fin) != 0u) {
-            const uint32_t slot = entry & ~PT_WF_SHADOW_BIT;
-            bool hit = false, miss = false;
-            if (fin) {
-                if (Cfg::COUNT) atomicAdd(sc.ray_histogram + (steps ? 32 - __clz(steps) : 0), 1ull);
-                if (!anyhit && tie) { cnt.tie(); res = trace_wide_fallback(sc, r.o, r.d); }     // exact tie: let the reference order decide
-                if (anyhit) {
-                    if (res.tri >= 0) wf.cs[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
-                } else if (res.tri >= 0) {
-                    wf.hit[slot] = make_int2(res.tri | (res.inside ? (int)0x80000000 : 0), __float_as_int(res.t));
-                    hit = true;
-                } else {
-                    miss = true;
-                }
-                have = false;
-            }
-            wf_stage_add(sh, hit, slot, wf.q_hit, wf_ctr(wf, WF_C_HIT_TAIL, b));
-            wf_stage_add(sm, miss, slot, wf.q_miss[b & 1], wf_ctr(wf, WF_C_MISS_TAIL, b));
         }
     }
 }
@@ -477,33 +455,55 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
 template <class Cfg>
 __global__ void __launch_bounds__(256, PT_WF_TRACE_CTAS) wf_trace(const __grid_constant__ RenderParams p, int b) {
     const WaveBuffers& wf = p.wf;
-    __shared__ uint32_t s_stage[2][8][64];
 #if PT_SMEM_STACK > 0
     __shared__ uint32_t s_stack[PT_SMEM_STACK * PT_STACK_STRIDE];
     uint32_t* const smem_stack = s_stack;
 #else
     uint32_t* const smem_stack = nullptr;
 #endif
-    const int warp = threadIdx.x >> 5;
-    WfStage sh, sm;
-    sh.buf = s_stage[0][warp]; sh.n = 0;
-    sm.buf = s_stage[1][warp]; sm.n = 0;
     const uint32_t count = *wf_ctr(wf, WF_C_RAY_TAIL, b);
     uint32_t nrays = 0;
     Counter<Cfg::COUNT> cnt;
-    if (Cfg::FAST_TREE) wf_trace_refill<Cfg>(p, b, count, sh, sm, smem_stack, nrays, cnt);
-    else wf_trace_simple<Cfg>(p, b, count, sh, sm, nrays, cnt);
-    wf_stage_flush(sh, wf.q_hit, wf_ctr(wf, WF_C_HIT_TAIL, b));
-    wf_stage_flush(sm, wf.q_miss[b & 1], wf_ctr(wf, WF_C_MISS_TAIL, b));
+    if (Cfg::FAST_TREE) wf_trace_refill<Cfg>(p, b, count, smem_stack, nrays, cnt);
+    else wf_trace_simple<Cfg>(p, b, count, nrays, cnt);
     wf_flush_rays(nrays, p.ray_counter);
     flush_counts(cnt, p.work_counters);
+}
+
+// ---- classify: results of bounce b -> what the paths need -------------------------------------------------------------
+// A streaming pass over the ray queue (12 bytes in per ray, full warps): an occluded shadow ray zeroes its path's pending
+// light term; a bounce ray that hit leaves its hit record with the path and the path joins Q_hit, one that escaped Q_miss.
+static __global__ void __launch_bounds__(256) wf_classify(const __grid_constant__ RenderParams p, int b) {
+    const WaveBuffers& wf = p.wf;
+    const uint32_t count = *wf_ctr(wf, WF_C_RAY_TAIL, b);
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < count; i0 += stride) {          // whole warps stay together for the ballots
+        const uint32_t i = i0 + threadIdx.x;
+        bool hit = false, miss = false;
+        uint32_t slot = 0;
+        if (i < count) {
+            const uint32_t e = wf.q_ray[i];
+            const int2 r = wf.res[i];
+            slot = e & ~PT_WF_SHADOW_BIT;
+            if (e & PT_WF_SHADOW_BIT) {
+                if (r.x != -1) wf.cs[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+            } else if (r.x != -1) {
+                wf.hit[slot] = r;
+                hit = true;
+            } else {
+                miss = true;
+            }
+        }
+        wf_push(wf.q_hit, wf_ctr(wf, WF_C_HIT_TAIL, b), hit, slot);
+        wf_push(wf.q_miss[b & 1], wf_ctr(wf, WF_C_MISS_TAIL, b), miss, slot);
+    }
 }
 
 // ---- shade: what trace(b-1) resolved ---------------------------------------------------------------------------------
 // phase 1: Q_hit[b-1] — the bounce ray hit: emissive term, history, then bounce b;  phase 2: Q_miss[b-1] — it escaped (or
 // never flew): environment term, path done.  Both lists are compact: full warps in either phase.
 template <class Cfg, int VARIANT>
-__global__ void __launch_bounds__(256) wf_shade(const __grid_constant__ RenderParams p, uint32_t f0, int b) {
+__global__ void __launch_bounds__(256, PT_WF_HEAD_CTAS) wf_shade(const __grid_constant__ RenderParams p, uint32_t f0, int b) {
     typedef typename Cfg::M M;
     const WaveBuffers& wf = p.wf;
     const DevScene& sc = p.sc;
@@ -527,10 +527,11 @@ __global__ void __launch_bounds__(256) wf_shade(const __grid_constant__ RenderPa
                     tr.tri = hr.x & 0x7fffffff; tr.inside = hr.x < 0; tr.t = __int_as_float(hr.y);
                     V3 Lo = xyz(lo4);
                     if (__float_as_uint(fr.w) & PT_WF_FLAG_SHADOW) Lo = Lo + xyz(wf.cs[slot]);            // the light term of bounce b-1, in order
-                    const uint32_t fl = slot / wf.npix, idx = slot - fl * wf.npix;
+                    const uint32_t islot = wf.pix[slot];
+                    const uint32_t fl = islot / wf.npix, idx = islot - fl * wf.npix;
                     const int px = (int)(idx % (uint32_t)p.width), py = (int)(idx / (uint32_t)p.width);
                     const uint32_t frame = p.first_frame + (f0 + fl) * p.frame_stride;
-                    nx = wf_shade_hit<Cfg, VARIANT>(p, slot, px, py, frame, p.sobol_tab ? p.sobol_tab + (size_t)(f0 + fl) * 8 : nullptr, b, xyz(ro), xyz(rd), tr,
+                    nx = wf_shade_hit<Cfg, VARIANT>(p, slot, islot, px, py, frame, p.sobol_tab ? p.sobol_tab + (size_t)(f0 + fl) * 8 : nullptr, b, xyz(ro), xyz(rd), tr,
                                                     xyz(hs), Lo, xyz(fr), rd.w, ro.w, __float_as_uint(hs.w), __float_as_int(lo4.w), cnt);
                 }
                 wf_push2(wf.q_ray, wf_ctr(wf, WF_C_RAY_TAIL, b), nx.shadow, slot | PT_WF_SHADOW_BIT, nx.extend, slot);
@@ -570,7 +571,7 @@ __global__ void __launch_bounds__(256) wf_shade(const __grid_constant__ RenderPa
                         Lo = Lo + history * sky * f_r * cosw / pdf;
                     }
                 }
-                wf_finish<Cfg>(p, slot, Lo, __float_as_int(lo4.w));
+                wf_finish<Cfg>(p, wf.pix[slot], Lo, __float_as_int(lo4.w));
             }
         }
     }
@@ -593,7 +594,7 @@ __global__ void __launch_bounds__(256) wf_accumulate(const __grid_constant__ Ren
         const size_t idx = (size_t)py * p.width + px;
         float4 acc = p.accum[idx];
         for (uint32_t fl = 0; fl < nf; fl++) {
-            const float4 c = wf.lo[(size_t)fl * wf.npix + idx];
+            const float4 c = wf.img[(size_t)fl * wf.npix + idx];
             if (p.accumulate_sum) {
                 acc.x = s_add(acc.x, c.x); acc.y = s_add(acc.y, c.y); acc.z = s_add(acc.z, c.z);
             } else {                                      // mix(lastColor, color, 1/(frameCounter+1)), P:868-869
@@ -607,43 +608,73 @@ __global__ void __launch_bounds__(256) wf_accumulate(const __grid_constant__ Ren
         acc.w = 1.0f;
         p.accum[idx] = acc;
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(p.ray_counter, (unsigned long long)*wf_misc_ctr(wf, 3));   // the wave's primary rays
 }
 
 // ---- host side: wave after wave on the context's stream ---------------------------------------------------------------
-// launches per wave (the counter memset is not a kernel): head + max_bounce x (trace + shade) + accumulate
-__host__ inline int wavefront_launches_per_wave(int max_bounce) { return 2 + 2 * max_bounce; }
-__host__ inline uint32_t wavefront_frames_per_wave(const WaveBuffers& wf) { return (uint32_t)(wf.cap / wf.npix > 0 ? wf.cap / wf.npix : 1); }
+// launches per wave (the counter memset is not a kernel): head + max_bounce x (trace + classify + shade) + accumulate
+__host__ inline int wavefront_launches_per_wave(int max_bounce) { return 2 + 3 * max_bounce; }
 
+// Frames per wave.  Safe start: every owned pixel of every frame could survive, so F0 = pcap / owned pixels (and never more
+// image slots than icap).  After each wave the host knows the survivor fraction and sizes the next wave to fill 3/4 of the
+// path slots; a wave that still runs out of slots (overflow flag) is repeated with half the frames — nothing has been
+// folded into the framebuffer at that point.  One stream synchronisation per wave (tens of ms of GPU work).
+struct WaveStats { unsigned long long waves = 0, retries = 0, frames = 0; };
 template <class Cfg, int VARIANT>
-cudaError_t launch_wavefront_variant(const RenderParams& p, int num_sms, cudaStream_t stream) {
+cudaError_t launch_wavefront_variant(const RenderParams& p, int num_sms, cudaStream_t stream, WaveStats* ws) {
     const WaveBuffers& wf = p.wf;
     const int mb = p.max_bounce;
-    const uint32_t F = wavefront_frames_per_wave(wf);
+    const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
+    const size_t owned = (size_t)tm.count() * 32;                            // upper bound of the pixels this launch renders per frame
+    if (owned == 0) return cudaSuccess;
+    const uint32_t f_img = (uint32_t)(wf.icap / wf.npix);                    // frames the image-slot array holds
+    uint32_t F = (uint32_t)std::min<size_t>(f_img, std::max<size_t>(1, wf.pcap / owned));
     if (VARIANT == 2 && p.sobol_tab)
         sobol_table_kernel<<<(p.n_frames * 8 + 255) / 256, 256, 0, stream>>>(const_cast<float*>(p.sobol_tab), p.first_frame, p.n_frames, p.frame_stride);
-    int per_sm = 0;
+    int per_sm = 0, per_sm_head = 0, per_sm_shade = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wf_trace<Cfg>, 256, 0);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_head, wf_head<Cfg, VARIANT>, 256, 0);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, wf_shade<Cfg, VARIANT>, 256, 0);
     if (e != cudaSuccess) return e;
-    const int grid_trace = num_sms * (per_sm > 0 ? per_sm : 1), grid = num_sms * 5;
-    for (uint32_t f0 = 0; f0 < p.n_frames; f0 += F) {
-        const uint32_t nf = p.n_frames - f0 < F ? p.n_frames - f0 : F;
+    const int grid_trace = num_sms * (per_sm > 0 ? per_sm : 1), grid_head = num_sms * (per_sm_head > 0 ? per_sm_head : 1),
+              grid_shade = num_sms * (per_sm_shade > 0 ? per_sm_shade : 1), grid = num_sms * 8;
+    uint32_t f0 = 0;
+    while (f0 < p.n_frames) {
+        const uint32_t nf = std::min(p.n_frames - f0, F);
         e = cudaMemsetAsync(wf.counters, 0, (size_t)PT_WF_NUM_CTRS * PT_WF_CTR_STRIDE * sizeof(uint32_t), stream);
         if (e != cudaSuccess) return e;
-        wf_head<Cfg, VARIANT><<<grid, 256, 0, stream>>>(p, f0, nf);
+        wf_head<Cfg, VARIANT><<<grid_head, 256, 0, stream>>>(p, f0, nf);
+        uint32_t paths = 0, overflow = 0;
+        e = cudaMemcpyAsync(&paths, wf_misc_ctr(wf, 1), sizeof paths, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&overflow, wf_misc_ctr(wf, 2), sizeof overflow, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess) return e;
+        if (overflow) {                                                       // only reachable after F grew on an optimistic estimate
+            F = std::max(1u, nf / 2u);
+            if (ws) ws->retries++;
+            continue;
+        }
         for (int b = 0; b < mb; b++) {
             wf_trace<Cfg><<<grid_trace, 256, 0, stream>>>(p, b);
-            wf_shade<Cfg, VARIANT><<<grid, 256, 0, stream>>>(p, f0, b + 1);
+            wf_classify<<<grid, 256, 0, stream>>>(p, b);
+            wf_shade<Cfg, VARIANT><<<grid_shade, 256, 0, stream>>>(p, f0, b + 1);
         }
         wf_accumulate<Cfg><<<grid, 256, 0, stream>>>(p, f0, nf);
+        if (ws) { ws->waves++; ws->frames += nf; }
+        f0 += nf;
+        // next wave: fill 3/4 (WaveBuffers.fill) of the path slots at the survivor rate just measured
+        const double per_frame = std::max(1.0, (double)paths / (double)nf);
+        const double want = (double)wf.fill * (double)wf.pcap / per_frame;
+        F = (uint32_t)std::min<double>((double)f_img, std::max(1.0, want));
     }
     return cudaGetLastError();
 }
 
 template <class Cfg>
-cudaError_t launch_wavefront(const RenderParams& p, int variant, int num_sms, cudaStream_t stream) {
-    if (variant == 0) return launch_wavefront_variant<Cfg, 0>(p, num_sms, stream);
-    if (variant == 1) return launch_wavefront_variant<Cfg, 1>(p, num_sms, stream);
-    return launch_wavefront_variant<Cfg, 2>(p, num_sms, stream);
+cudaError_t launch_wavefront(const RenderParams& p, int variant, int num_sms, cudaStream_t stream, WaveStats* ws) {
+    if (variant == 0) return launch_wavefront_variant<Cfg, 0>(p, num_sms, stream, ws);
+    if (variant == 1) return launch_wavefront_variant<Cfg, 1>(p, num_sms, stream, ws);
+    return launch_wavefront_variant<Cfg, 2>(p, num_sms, stream, ws);
 }
 
 }  // namespace pt

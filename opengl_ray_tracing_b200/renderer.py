@@ -22,10 +22,12 @@ MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE, MODE_PARITY_FAST, MODE_FAST_COUNT 
 DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 
 ACC_MEAN, ACC_SUM = 0, 1
+COMBINE_SUM, COMBINE_DISJOINT = 0, 1
+COMM_ID_BYTES = 128
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
-           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_measure_l2_read_gbs", "pt_last_error",
+           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_measure_l2_read_gbs", "pt_kernel_sass_hash", "pt_comm_get_unique_id", "pt_comm_init", "pt_comm_info", "pt_comm_destroy", "pt_combine", "pt_last_error",
            "pt_build_info"]
 
 
@@ -80,6 +82,12 @@ def lib():
         "pt_get_ray_histogram": (C.c_int, [vp, C.POINTER(C.c_ulonglong), C.c_int]),
         "pt_last_error": (C.c_char_p, []),
         "pt_build_info": (C.c_char_p, []),
+        "pt_kernel_sass_hash": (C.c_char_p, []),
+        "pt_comm_get_unique_id": (C.c_int, [vp, C.c_size_t]),
+        "pt_comm_init": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_size_t]),
+        "pt_comm_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+        "pt_comm_destroy": (C.c_int, [vp]),
+        "pt_combine": (C.c_int, [vp, C.c_int, C.c_uint, vp, vp]),
         "pt_calculate_hdr_cache": (C.c_int, [C.c_int, C.POINTER(C.c_float), C.c_int, C.c_int, C.POINTER(C.c_float)]),
         "pt_measure_l2_read_gbs": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     }
@@ -203,6 +211,32 @@ class PathTracer:
     def scale_framebuffer(self, scale):
         _check(lib().pt_scale_framebuffer(self._h, scale), "pt_scale_framebuffer")
 
+    # ---- multi-GPU (pt_comm.cu) ----
+    def comm_init(self, world, rank, unique_id: bytes):
+        """Collective over the `world` contexts; unique_id = comm_unique_id() of rank 0, passed around by the caller."""
+        buf = C.create_string_buffer(bytes(unique_id), COMM_ID_BYTES)
+        _check(lib().pt_comm_init(self._h, world, rank, C.cast(buf, C.c_void_p), COMM_ID_BYTES), "pt_comm_init")
+
+    def comm_info(self):
+        w, r, p = C.c_int(), C.c_int(), C.c_int()
+        _check(lib().pt_comm_info(self._h, C.byref(w), C.byref(r), C.byref(p)), "pt_comm_info")
+        return {"world": w.value, "rank": r.value, "peer_memory": bool(p.value)}
+
+    def combine(self, kind, total_frames=0, out_ptr=None, display_ptr=None):
+        """Collective: all ranks' framebuffers -> one image on rank 0 (pt_combine).  out_ptr / display_ptr: host addresses or None."""
+        _check(lib().pt_combine(self._h, kind, total_frames, out_ptr, display_ptr), "pt_combine")
+
+    def combine_readback(self, kind, total_frames=0, display=False):
+        """Rank 0: returns the combined float32 [H, W, 4] image (and the uint8 display image); other ranks: None."""
+        info = self.comm_info()
+        if info["rank"] != 0:
+            self.combine(kind, total_frames)
+            return None
+        img = np.empty((self.height, self.width, 4), np.float32)
+        disp = np.empty((self.height, self.width, 4), np.uint8) if display else None
+        self.combine(kind, total_frames, img.ctypes.data, disp.ctypes.data if display else None)
+        return (img, disp) if display else img
+
     def stats(self) -> dict:
         st = PtStats()
         _check(lib().pt_get_stats(self._h, C.byref(st)), "pt_get_stats")
@@ -220,6 +254,16 @@ class PathTracer:
 
 def build_info() -> str:
     return lib().pt_build_info().decode()
+
+
+def comm_unique_id() -> bytes:
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    _check(lib().pt_comm_get_unique_id(C.cast(buf, C.c_void_p), COMM_ID_BYTES), "pt_comm_get_unique_id")
+    return buf.raw
+
+
+def kernel_sass_hash() -> str:
+    return lib().pt_kernel_sass_hash().decode()
 
 
 def measure_l2_read_gbs(device=0, window_mb=48, passes=64):

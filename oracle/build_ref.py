@@ -8,7 +8,10 @@ box like the product's own).  The reference's own build system (Visual Studio .v
 Outputs:
   libref_host.so                 host functions of IS/main.cpp + hdrloader.cpp  (see ref_host_wrap.cpp)
   libref_shader_<v>_<math>.so    the reference pass1.fsh of variant v in {ogl, disney, is} compiled as
-                                 C++ (see glsl_compat.h / ref_shader_wrap.cpp); math in {libm, ptmath}
+                                 C++ (see glsl_compat.h / ref_shader_wrap.cpp); math in {libm, ptmath} are the
+                                 parity builds (-O2 -ffp-contract=off); math = libmO3 is the TIMING build of SURVEY.md 8d
+                                 (g++ -O3 -fopenmp, libm) that bench.py --impl reference runs
+  libref_pass3.so                shaders/pass3.fsh (the display pass) compiled the same way
   basic_tracer                   BasicRayTracingWithC++/main.cpp, g++ -O3 -fopenmp, SAMPLE overridable
                                  through the REF_SAMPLE macro (the only edit: `const int SAMPLE = 128`)
   libref_basic_det.so            the same source with a reproducible random stream, as a library (ref_basic_wrap.cpp)
@@ -81,11 +84,12 @@ def build_shaders():
             text = shader_to_cpp(f.read())
         with open(inc, "w", encoding="latin-1") as f:
             f.write(text)
-        for math in ("libm", "ptmath"):
+        for math in ("libm", "ptmath", "libmO3"):
             so = os.path.join(OUT, "libref_shader_%s_%s.so" % (name, math))
             if newer(so, path, wrap, compat, os.path.join(INC, "ptmath.h"), __file__):
                 continue
-            cmd = ["g++", *CXXFLAGS, "-shared", "-I", HERE, "-I", INC,
+            flags = ["-std=c++17", "-O3", "-fopenmp", "-fPIC", "-w"] if math == "libmO3" else CXXFLAGS
+            cmd = ["g++", *flags, "-shared", "-I", HERE, "-I", INC,
                    '-DREF_SHADER_INC="%s"' % inc, "-DREF_VARIANT=%d" % variant]
             if math == "ptmath":
                 cmd.append("-DREF_MATH_PTMATH")

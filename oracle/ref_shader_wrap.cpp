@@ -67,6 +67,13 @@ using namespace glslc;
 extern "C" {
 
 int ref_shader_variant(void) { return REF_VARIANT; }
+int ref_shader_num_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
 
 /* NDC coordinate of fragment centre k on an n-pixel axis (rasteriser interpolation of the quad's
    vPosition, vshader.vsh:7-8); this formula is the one definition shared with oracle/ptoracle.cpp and
@@ -95,9 +102,14 @@ int ref_shader_render(const float* tris, int nTriangles, const float* nodes, int
         u.eye = vec3(eye[0], eye[1], eye[2]);
         for (int c = 0; c < 4; c++)                                      /* column-major, glm value_ptr */
             u.cameraRotate.c[c] = vec4(cameraRotate[4*c], cameraRotate[4*c+1], cameraRotate[4*c+2], cameraRotate[4*c+3]);
-        #pragma omp parallel for schedule(dynamic, 4)
-        for (int y = y0; y < y1; y++) {
-            for (int x = x0; x < x1; x++) {
+        /* fragments are independent; runs of 16 pixels of a row per task: a mesh row costs ~100x a sky row, so whole rows
+           (the round-1 schedule) left most threads idle behind the few that drew the mesh rows */
+        const int rw = x1 - x0, runs_per_row = (rw + 15) / 16;
+        const long n_runs = (long)runs_per_row * (y1 - y0);
+        #pragma omp parallel for schedule(dynamic, 1)
+        for (long run = 0; run < n_runs; run++) {
+            const int y = y0 + (int)(run / runs_per_row), xa = x0 + (int)(run % runs_per_row) * 16, xb = xa + 16 < x1 ? xa + 16 : x1;
+            for (int x = xa; x < xb; x++) {
                 Fragment frag(u, vec3(ndc_of(x, width), ndc_of(y, height), 0.0f));
                 frag.main();
                 float* o = accum + 4 * ((size_t)y * width + x);

@@ -116,9 +116,11 @@ def test_config5_full_10M_4k_ids_and_tile_split(R):
     assert 0.2 < (ids_ref >= 0).mean()
     img, ids, _ = gpu_crop(R, sc, W, H, reg, 0, 1, R.MODE_PARITY_FAST)
     assert (ids == ids_ref).all() and img.tobytes() == ref.tobytes()
+    ref2, ids_ref2 = oracle_crop(sc, W, H, reg, 0, 2)          # ids are those of the LAST frame rendered
     one, ids1, _ = gpu_crop(R, sc, W, H, reg, 0, 2, R.MODE_FAST)
     split, ids8, st = gpu_crop(R, sc, W, H, reg, 0, 2, R.MODE_FAST, tiles_of_world=8)
-    assert (ids1 == ids_ref).all() and (ids8 == ids_ref).all()
+    assert (ids1 == ids_ref2).all() and (ids8 == ids_ref2).all()
+    assert rrmse(one, ref2) <= RRMSE_TOL
     assert split.tobytes() == one.tobytes(), "the 8-way tile split must be bit-identical to one GPU"
     assert st["samples"] == 2 * 256 * 144
 

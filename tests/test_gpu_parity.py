@@ -293,21 +293,27 @@ def test_metric_scene_every_pipeline(R):
 
 
 def test_wavefront_waves_and_lane_refill(R, monkeypatch):
-    """The wavefront pipeline renders F = capacity / pixels frames per wave; with 1 Mi path slots a 512x512 image gets 4
-    frames per wave, so 10 frames are three waves (4, 4, 2): bit-identical to the megakernel, also as two launches."""
+    """The wavefront pipeline sizes its waves from the path-slot capacity: with 1 Mi slots a 512x512 image starts at 4 frames
+    per wave, then grows to what the survivors of the first wave allow; 24 frames are several waves.  Bit-identical to the
+    megakernel, also as two launches, also when an over-optimistic fill target forces waves to be repeated."""
     monkeypatch.setenv("PT_WF_PATHS_M", "1")
     for kind in ("is", "disney"):
         sc = small_scene(kind, "10k", hdr_res=(256, 128), camera=(10.0, 25.0, 2.5))
         W = H = 512
-        ref, ids_ref, st_ref, _ = render(R, sc, W, H, 0, 10, R.MODE_PARITY_FAST, pipeline=R.MEGAKERNEL)
-        img, ids, st, _ = render(R, sc, W, H, 0, 10, R.MODE_PARITY_FAST, pipeline=R.WAVEFRONT)
+        NF = 24
+        ref, ids_ref, st_ref, _ = render(R, sc, W, H, 0, NF, R.MODE_PARITY_FAST, pipeline=R.MEGAKERNEL)
+        img, ids, st, _ = render(R, sc, W, H, 0, NF, R.MODE_PARITY_FAST, pipeline=R.WAVEFRONT)
         assert img.tobytes() == ref.tobytes() and (ids == ids_ref).all() and st["rays"] == st_ref["rays"]
-        assert st["launches"] >= 3 * (2 + 2 * sc.max_bounce)
-        img, _, _, pt = render(R, sc, W, H, 0, 7, R.MODE_PARITY_FAST, pipeline=R.WAVEFRONT, close=False)
-        img, ids, _, _ = render(R, sc, W, H, 7, 3, R.MODE_PARITY_FAST, pt=pt)
+        assert st["launches"] >= 2 * (2 + 3 * sc.max_bounce)
+        img, _, _, pt = render(R, sc, W, H, 0, 17, R.MODE_PARITY_FAST, pipeline=R.WAVEFRONT, close=False)
+        img, ids, _, _ = render(R, sc, W, H, 17, NF - 17, R.MODE_PARITY_FAST, pt=pt)
         assert img.tobytes() == ref.tobytes() and (ids == ids_ref).all()
-        fast, ids_f, _, _ = render(R, sc, W, H, 0, 10, R.MODE_FAST, pipeline=R.WAVEFRONT)
+        fast, ids_f, _, _ = render(R, sc, W, H, 0, NF, R.MODE_FAST, pipeline=R.WAVEFRONT)
         assert (ids_f == ids_ref).all() and rrmse(fast, ref) <= RRMSE_TOL
+        monkeypatch.setenv("PT_WF_FILL_PCT", "400")            # the host aims at 4x the slots there are: waves overflow and are repeated
+        img, ids, st, _ = render(R, sc, W, H, 0, NF, R.MODE_PARITY_FAST, pipeline=R.WAVEFRONT)
+        monkeypatch.delenv("PT_WF_FILL_PCT")
+        assert img.tobytes() == ref.tobytes() and (ids == ids_ref).all() and st["rays"] == st_ref["rays"]
 
 
 def test_counting_build_and_cost_map(R):

@@ -14,17 +14,23 @@ defs = [d for d in defs if d != "--fast-only"]
 if "--no-base" not in defs:
     B.build_pt()
 defs = [d for d in defs if d != "--no-base"]
+fast_flags = ["-prec-div=false", "-prec-sqrt=false"]
+for d in list(defs):
+    if d.startswith("--fast-flags="):         # replaces the production TU's floating-point flags, e.g. --fast-flags=-fmad=false
+        fast_flags = d.split("=", 1)[1].split()
+        defs.remove(d)
 vdir = os.path.join(B.BUILD, "variant_" + name)
 os.makedirs(vdir, exist_ok=True)
 objs = []
-for unit, extra in (("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", ["-prec-div=false", "-prec-sqrt=false"])):
+for unit, extra in (("pt_kernels_parity", ["-fmad=false"]), ("pt_kernels_fast", fast_flags)):
     if fast_only and unit == "pt_kernels_parity":
         objs.append(os.path.join(B.BUILD, unit + ".o"))
         continue
     obj = os.path.join(vdir, unit + ".o")
     B._run(["nvcc", *B.ARCH, *B.NVCC_COMMON, *extra, *defs, "-c", os.path.join(B.CSRC, unit + ".cu"), "-o", obj], log=os.path.join(vdir, unit + ".ptxas.log"))
     objs.append(obj)
-objs += [os.path.join(B.BUILD, u + ".o") for u in ("pt_api", "pt_hdrcache", "pt_basic", "pt_probe", "pt_build")]
+objs.append(B._sass_hash_object(objs[:2], force=True) if not fast_only else os.path.join(B.BUILD, "pt_sasshash.o"))
+objs += [os.path.join(B.BUILD, u + ".o") for u in ("pt_api", "pt_hdrcache", "pt_basic", "pt_probe", "pt_comm", "pt_build")]
 out = os.path.join(B.HERE, "libpt_%s.so" % name)
-B._run(["nvcc", *B.ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-lgomp", "-o", out])
+B._run(["nvcc", *B.ARCH, "-shared", "-Xcompiler", "-fPIC", *objs, "-lgomp", "-ldl", "-o", out])
 print(out)
