@@ -177,18 +177,20 @@ int pt_comm_get_unique_id(void* id, size_t bytes);
 int pt_comm_init(pt_ctx* ctx, int world, int rank, const void* id, size_t bytes);
 int pt_comm_info(pt_ctx* ctx, int* world, int* rank, int* peer_memory);    /* peer_memory = 1: the one-kernel NVLink path is active */
 int pt_comm_destroy(pt_ctx* ctx);
-/* Collective: combines the framebuffers of all ranks into ONE image on rank 0.
-   kind = PT_COMBINE_SUM       sample split: every rank rendered its frames with PT_ACC_SUM; result rgb = sum / total_frames
-   kind = PT_COMBINE_DISJOINT  tile split: every rank rendered its own tiles (pt_set_tile_interleave / band / region) as the
-                               running mean; the sum of disjoint regions is exact (x + 0), i.e. bit-identical to one GPU
-   Alpha = 1 (P:871).  One kernel per GPU: rank r loads slice r of all framebuffers over NVLink, applies the scale (and for
-   rgba8 the pass3 tone map, shaders/pass3.fsh:14-24) and stores into rank 0's image; rank 0 then copies to rgba_host
-   (W*H float4, row 0 = bottom) and/or rgba8_host (W*H RGBA8, row 0 = top) — either may be NULL; other ranks pass NULL.
-   Each rank's own framebuffer is left untouched, so rendering can continue and be combined again.  Synchronises on rank 0
-   when a host buffer is given. */
+/* Collective: combines the framebuffers of all ranks into ONE image on rank 0.  flags (the same on every rank):
+     PT_COMBINE_SUM       sample split: every rank rendered its frames with PT_ACC_SUM; result rgb = sum / total_frames
+     PT_COMBINE_DISJOINT  tile split: every rank rendered its own tiles (pt_set_tile_interleave / band / region) as the
+                          running mean; the sum of disjoint regions is exact (x + 0), i.e. bit-identical to one GPU
+     | PT_COMBINE_DISPLAY also produce the 8-bit display image (the pass3 tone map, shaders/pass3.fsh:14-24, in the same kernel)
+   Alpha = 1 (P:871).  One kernel per GPU: rank r loads slice r of all framebuffers over NVLink, applies the scale (and the
+   tone map) and stores into rank 0's image, between two NCCL barriers on the contexts' streams.  Rank 0 may pass rgba_host
+   (W*H float4, row 0 = bottom) and/or rgba8_host (W*H RGBA8, row 0 = top; needs PT_COMBINE_DISPLAY) to receive the result,
+   and then synchronises; with both NULL the call is asynchronous on every rank.  Each rank's own framebuffer is left
+   untouched, so rendering can continue and be combined again.  world = 1 runs the same epilogue on the one framebuffer. */
 #define PT_COMBINE_SUM      0
 #define PT_COMBINE_DISJOINT 1
-int pt_combine(pt_ctx* ctx, int kind, unsigned total_frames, float* rgba_host, unsigned char* rgba8_host);
+#define PT_COMBINE_DISPLAY  4
+int pt_combine(pt_ctx* ctx, int flags, unsigned total_frames, float* rgba_host, unsigned char* rgba8_host);
 
 int pt_synchronize(pt_ctx* ctx);
 int pt_get_stats(pt_ctx* ctx, PtStats* out);

@@ -256,61 +256,51 @@ int pt_comm_info(pt_ctx* c, int* world, int* rank, int* peer_memory) {
     return PT_OK;
 }
 
-int pt_combine(pt_ctx* c, int kind, unsigned total_frames, float* rgba_host, unsigned char* rgba8_host) {
+int pt_combine(pt_ctx* c, int flags, unsigned total_frames, float* rgba_host, unsigned char* rgba8_host) {
     if (!c) return fail(PT_EINVAL, "pt_combine: null context");
-    if (kind != PT_COMBINE_SUM && kind != PT_COMBINE_DISJOINT) return fail(PT_EINVAL, "pt_combine: kind must be PT_COMBINE_SUM or PT_COMBINE_DISJOINT");
+    const int kind = flags & 3;
+    const bool display = (flags & PT_COMBINE_DISPLAY) != 0;
+    if ((flags & ~(3 | PT_COMBINE_DISPLAY)) || (kind != PT_COMBINE_SUM && kind != PT_COMBINE_DISJOINT))
+        return fail(PT_EINVAL, "pt_combine: flags = PT_COMBINE_SUM or PT_COMBINE_DISJOINT, optionally | PT_COMBINE_DISPLAY");
     if (kind == PT_COMBINE_SUM && total_frames == 0) return fail(PT_EINVAL, "pt_combine: total_frames must be > 0 for PT_COMBINE_SUM");
+    if (rgba8_host && !display) return fail(PT_EINVAL, "pt_combine: rgba8_host needs PT_COMBINE_DISPLAY (on every rank)");
     CK(cudaSetDevice(c->cfg.device));
     const size_t npx = (size_t)c->cfg.width * c->cfg.height;
     const int W = c->cfg.width, H = c->cfg.height;
     const float scale = kind == PT_COMBINE_SUM ? 1.0f / (float)total_frames : 1.0f;
     const int scale_rgb = kind == PT_COMBINE_SUM ? 1 : 0;
     PtComm* m = c->comm;
+    if (!m) return fail(PT_EINVAL, "pt_combine: pt_comm_init first (world = 1 is allowed)");
+    if (m->rank != 0 && (rgba_host || rgba8_host)) return fail(PT_EINVAL, "pt_combine: only rank 0 receives the image");
     const int grid = (c->num_sms > 0 ? c->num_sms : 148) * 4;
-    if (!m || m->world == 1) {
-        // one GPU: the same consumer epilogue over the context's own framebuffer (a PT_ACC_SUM render divided, or a no-op scale)
-        if (!c->display) CK(cudaMalloc(&c->display, npx * sizeof(uchar4)));
+    if (m->world == 1) {
+        // one GPU: the same consumer epilogue over the context's own framebuffer
         PeerTable t; std::memset(&t, 0, sizeof t); t.fb[0] = c->accum;
-        float4* out = nullptr;
-        if (m) out = m->my_f4;
-        else if (rgba_host) return fail(PT_EINVAL, "pt_combine: without pt_comm_init use pt_scale_framebuffer + pt_readback");
-        k_combine<<<grid, 256, 0, c->stream>>>(t, 1, 0, npx, scale, scale_rgb, out, rgba8_host ? c->display : nullptr, W, H);
+        k_combine<<<grid, 256, 0, c->stream>>>(t, 1, 0, npx, scale, scale_rgb, m->my_f4, display ? m->my_u8 : nullptr, W, H);
         CK(cudaGetLastError());
         c->launches += 1;
-        if (rgba_host) CK(cudaMemcpyAsync(rgba_host, out, npx * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
-        if (rgba8_host) CK(cudaMemcpyAsync(rgba8_host, c->display, npx * 4, cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaStreamSynchronize(c->stream));
-        return PT_OK;
-    }
-    const bool want_f4 = true, want_u8 = rgba8_host != nullptr || false;
-    // every rank must take the same branches: whether display bytes are produced is decided by rank 0's request, carried by the barrier
-    int req = (m->rank == 0 && rgba8_host) ? 1 : 0;
-    CK(cudaMemcpyAsync(m->token, &req, sizeof req, cudaMemcpyHostToDevice, c->stream));
-    NCK(m->api->AllReduce(m->token, m->token, 1, ncclInt, ncclMax, m->nccl, c->stream));   // barrier A: every render kernel is complete
-    int any_u8 = 0;
-    CK(cudaMemcpyAsync(&any_u8, m->token, sizeof any_u8, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    (void)want_u8;
-    if (m->peer) {
+    } else if (m->peer) {
+        // barrier A: every rank's render kernel is complete (stream order on every rank + the collective)
+        NCK(m->api->AllReduce(m->token, m->token, 1, ncclInt, ncclMax, m->nccl, c->stream));
         const size_t begin = npx * (size_t)m->rank / (size_t)m->world, end = npx * (size_t)(m->rank + 1) / (size_t)m->world;
-        k_combine<<<grid, 256, 0, c->stream>>>(m->table, m->world, begin, end, scale, scale_rgb, want_f4 ? m->out_f4 : nullptr,
-                                               any_u8 ? m->out_u8 : nullptr, W, H);
+        k_combine<<<grid, 256, 0, c->stream>>>(m->table, m->world, begin, end, scale, scale_rgb, m->out_f4, display ? m->out_u8 : nullptr, W, H);
         CK(cudaGetLastError());
         c->launches += 1;
-        NCK(m->api->AllReduce(m->token, m->token, 1, ncclInt, ncclMax, m->nccl, c->stream));   // barrier B: all slices have landed in rank 0's images
+        // barrier B: all slices have landed in rank 0's images, and nobody reads a framebuffer any more
+        NCK(m->api->AllReduce(m->token, m->token, 1, ncclInt, ncclMax, m->nccl, c->stream));
     } else {
         NCK(m->api->Reduce(c->accum, m->reduced, npx * 4, ncclFloat, ncclSum, 0, m->nccl, c->stream));
         if (m->rank == 0) {
             PeerTable t; std::memset(&t, 0, sizeof t); t.fb[0] = m->reduced;
-            k_combine<<<grid, 256, 0, c->stream>>>(t, 1, 0, npx, scale, scale_rgb, m->my_f4, any_u8 ? m->my_u8 : nullptr, W, H);
+            k_combine<<<grid, 256, 0, c->stream>>>(t, 1, 0, npx, scale, scale_rgb, m->my_f4, display ? m->my_u8 : nullptr, W, H);
             CK(cudaGetLastError());
             c->launches += 1;
         }
     }
-    if (m->rank == 0) {
+    if (m->rank == 0 && (rgba_host || rgba8_host)) {
         if (rgba_host) CK(cudaMemcpyAsync(rgba_host, m->my_f4, npx * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
         if (rgba8_host) CK(cudaMemcpyAsync(rgba8_host, m->my_u8, npx * 4, cudaMemcpyDeviceToHost, c->stream));
-        if (rgba_host || rgba8_host) CK(cudaStreamSynchronize(c->stream));
+        CK(cudaStreamSynchronize(c->stream));
     }
     return PT_OK;
 }

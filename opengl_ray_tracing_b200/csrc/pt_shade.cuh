@@ -37,15 +37,13 @@ struct MathExact {                // include/ptmath.h: the oracle's definition o
     static __device__ __forceinline__ float cos_dir(float a) { return pt_cosf(a); }
     static __device__ __forceinline__ float pow_dir(float a, float b) { return pt_powf(a, b); }
 };
-// Production arithmetic: SFU approximations where CUDA has them — except for the three calls that build a sampled
-// DIRECTION (sin/cos of the azimuth in SampleBRDF and the uniform hemisphere, pow in SampleGTR1).  What separates the
-// production image from the oracle's at fixed spp is not smooth error but discrete flips (a NEAREST texel, a shadow
-// ray grazing an edge, a sign test) whose probability is proportional to the error of the ray directions: on the metric
-// scene (floor roughness 0.01) the oracle's own libm and ptmath flavours differ by 4.0e-4 rRMSE at 2 spp, the SFU's
-// 2^-21 absolute error on sin/cos made it 1.14e-3 — over the 1e-3 bar (tests/test_gpu_configs.py).  include/ptmath.h's
-// sin/cos/pow are accurate to an ulp and cost ~60 instructions per bounce.
+// Production arithmetic: SFU approximations where CUDA has them.  (`*_dir` = the calls that build a sampled direction;
+// PT_DIR_TRIG_EXACT = 1 routes them to include/ptmath.h.  Measured on the bench's crop of the metric scene, 2 spp, rRMSE
+// of PT_MODE_FAST against the oracle: 9.3e-6 with the exact functions, 1.09e-5 with the SFU's — no gain worth 4.8 % of
+// the frame time.  What DID separate the production image from the oracle's, 1.14e-3, was the cancellation inside the
+// lobe samplers: see SampleBRDF.)
 #ifndef PT_DIR_TRIG_EXACT
-#define PT_DIR_TRIG_EXACT 1
+#define PT_DIR_TRIG_EXACT 0
 #endif
 #ifndef PT_STRICT_SAMPLERS
 #define PT_STRICT_SAMPLERS 1
@@ -464,7 +462,11 @@ __device__ __forceinline__ V3 SampleBRDF(float xi_1, float xi_2, float xi_3, V3 
     // mirror-like surface (the metric scene's floor: alpha = 0.001, 1 - cos^2 ~ 1e-6) an ulp of cos_theta_h is 10 % of
     // sin_theta_h, i.e. the sampled direction moves by 1e-5 rad when the compiler fuses or approximates one operation —
     // enough to land on the neighbouring environment texel in ~1 % of the samples.  These few operations therefore run in
-    // the oracle's arithmetic (un-fused IEEE mul/add/div/sqrt) in EVERY mode, like the ray/triangle tests do.
+    // the oracle's arithmetic (un-fused IEEE mul/add/div/sqrt) in EVERY mode, like the ray/triangle tests do, and the
+    // material-derived a^2 - 1 they consume comes from the exact-arithmetic upload kernel.  Measured (tools/fast_rrmse.py,
+    // the bench's crop of the metric scene, 2 spp): rRMSE of PT_MODE_FAST against the oracle 1.14e-3 -> 1.1e-5, for no
+    // measurable time (21.3 Grays/s either way); un-fusing or un-approximating the REST of the shading arithmetic buys
+    // nothing more until all of it is exact (-fmad=false + IEEE div/sqrt: 4.4e-8, at 16.3 Grays/s).
     if (rd <= p_diffuse) {                                        // SampleCosineHemisphere
 #if PT_STRICT_SAMPLERS
         float r = s_sqrt(xi_1);

@@ -46,6 +46,9 @@ namespace pt {
 #ifndef PT_WF_TRACE_CTAS
 #define PT_WF_TRACE_CTAS 4        // resident CTAs (256 threads) per SM the traversal kernel is compiled for (4: 64 registers)
 #endif
+#ifndef PT_WF_NODE_BIAS
+#define PT_WF_NODE_BIAS 0         // wf_trace's vote: a node step runs when (lanes at nodes) + bias >= (lanes at triangles)
+#endif
 #ifndef PT_WF_HEAD_CTAS
 #define PT_WF_HEAD_CTAS 4         // same for wf_head / wf_shade (64 registers)
 #endif
@@ -318,11 +321,20 @@ __device__ __forceinline__ void wf_trace_simple(const RenderParams& p, int b, ui
     }
 }
 
-// Production topology: trace_fast's while-while loop (pt_trace.cuh — same tests, same order, same result per ray) with the
-// ray state per LANE.  At the top of every round the warp counts its free lanes (no ray, or ray finished); once there are
-// PT_WF_REFILL_MIN of them (or none is busy) the finished ones store their results and all free lanes take the next rays
-// of the warp's chunk of the queue, together — one pass through the ~70 instructions of result store + ray set-up per
-// PT_WF_REFILL_MIN rays instead of one per ray.  A lane without work carries ref = PT_REF_NONE through both loops.
+// Production topology: trace_fast's tests in trace_fast's order per ray (pt_trace.cuh: same result per ray, bit for bit), but
+// scheduled for a warp whose 32 lanes hold 32 UNRELATED rays:
+//   * every lane is in one of two modes — at an inner NODE (one 64-byte fetch + two slab tests), or at a TRIangle of a leaf
+//     (one 48-byte fetch + hitTriangle).  Each turn the warp VOTES (__ballot_sync / __popc) and runs the step the majority
+//     wants; the minority idles for that turn only.  (A while-while loop — descend until every lane has a leaf, then test —
+//     makes the whole warp wait for its freshest ray's ~25-level descent from the root: measured 5.5 of 32 lanes per
+//     instruction with refill, profiles/r02_wavefront.md.)
+//   * lanes whose ray is finished park their result; once PT_WF_REFILL_MIN lanes are free (or no lane is busy) they store the
+//     results and all free lanes take the next rays of the warp's chunk of the queue together — one pass through the ~70
+//     instructions of result store + ray set-up per PT_WF_REFILL_MIN rays.
+#define PT_WF_MODE_NONE 0
+#define PT_WF_MODE_NODE 1
+#define PT_WF_MODE_TRI 2
+#define PT_WF_MODE_DONE 3
 template <class Cfg>
 __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, uint32_t count, uint32_t* smem_stack, uint32_t& nrays,
                                                 Counter<Cfg::COUNT>& cnt) {
@@ -336,9 +348,8 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
     const uint32_t chunk = max(32u, min((uint32_t)PT_WF_CHUNK, (count / (gridDim.x * 8u * 4u)) & ~31u));
     uint32_t chunk_next = 0, chunk_end = 0;            // warp-uniform: the part of the queue this warp still owns
     bool more = true;                                  // the queue may hold unclaimed chunks
-    // per-lane ray: state 0 = none, 1 = in flight, 2 = finished (result not stored yet)
-    int state = 0;
-    uint32_t qi = 0;                                   // its queue position
+    int mode = PT_WF_MODE_NONE;
+    uint32_t qi = 0;                                   // queue position of this lane's ray
     bool anyhit = false;
     Ray r;
     r.o = r.d = r.inv = mk3(0, 0, 0);
@@ -350,19 +361,21 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
     uint32_t steps = 0;
     TravStack<PT_STACK> stk;
     stk.init(smem_stack);
-    uint32_t ref = PT_REF_NONE;
+    uint32_t ref = PT_REF_NONE;                        // NODE: the inner node to fetch
+    uint32_t ti = 0, tend = 0;                         // TRI: the next triangle of the leaf, and the leaf's end
     for (;;) {
+        const uint32_t m_node = __ballot_sync(0xffffffffu, mode == PT_WF_MODE_NODE), m_tri = __ballot_sync(0xffffffffu, mode == PT_WF_MODE_TRI);
+        const uint32_t busy = m_node | m_tri;
         // ---- store finished results, refill ----
         {
-            const uint32_t busy = __ballot_sync(0xffffffffu, state == 1);
             const uint32_t nfree = 32u - (uint32_t)__popc(busy);
             const bool can_fetch = more || chunk_next < chunk_end;
             if (busy == 0u || (nfree >= (uint32_t)PT_WF_REFILL_MIN && can_fetch)) {      // (queue exhausted: results wait for the warp's last ray)
-                if (state == 2) {
+                if (mode == PT_WF_MODE_DONE) {
                     if (Cfg::COUNT) atomicAdd(sc.ray_histogram + (steps ? 32 - __clz(steps) : 0), 1ull);
                     if (!anyhit && tie) { cnt.tie(); res = trace_wide_fallback(sc, r.o, r.d); }   // exact tie: let the reference order decide
                     wf.res[qi] = wf_pack_result(res);
-                    state = 0;
+                    mode = PT_WF_MODE_NONE;
                 }
                 uint32_t idle = ~busy;                 // every lane that is not in flight is free now
                 while (can_fetch) {
@@ -376,7 +389,7 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
                     const uint32_t n_idle = (uint32_t)__popc(idle);
                     const uint32_t take = min(n_idle, chunk_end - chunk_next);
                     const uint32_t rank = (uint32_t)__popc(idle & lt);
-                    if (state == 0 && rank < take) {
+                    if (mode == PT_WF_MODE_NONE && rank < take) {
                         qi = chunk_next + rank;
                         const uint32_t entry = wf.q_ray[qi], slot = entry & ~PT_WF_SHADOW_BIT;
                         anyhit = (entry & PT_WF_SHADOW_BIT) != 0;
@@ -387,67 +400,84 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
                         res.tri = -1; res.t = PT_INF; res.inside = false;
                         cull = PT_INF; tie = false; steps = 0;
                         stk.clear();
-                        ref = sc.root_fast;
-                        state = 1;
+                        const uint32_t root = sc.root_fast;
+                        if (ref_count(root) == 0) { ref = root; mode = PT_WF_MODE_NODE; }
+                        else { ti = ref_index(root); tend = ti + ref_count(root); mode = PT_WF_MODE_TRI; }
                         nrays++;
                     }
                     chunk_next += take;
                     if (take == n_idle) break;
-                    idle = __ballot_sync(0xffffffffu, state == 0);
+                    idle = __ballot_sync(0xffffffffu, mode == PT_WF_MODE_NONE);
                 }
-                if (__ballot_sync(0xffffffffu, state == 1) == 0u) break;      // nothing in flight and nothing left to fetch
+                if (__ballot_sync(0xffffffffu, mode == PT_WF_MODE_NODE || mode == PT_WF_MODE_TRI) == 0u) break;   // nothing in flight, nothing left
+                continue;                                                                                        // vote again with the new rays
             }
         }
-        // ---- one round of trace_fast: descend to a leaf, test it, pop ----
-        while (ref_count(ref) == 0) {
-            const float4* w = sc.wnodes_fast + 4 * (size_t)ref;
-            const float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
-            cnt.inner();
-            if (Cfg::COUNT) steps++;
-            float e1, e2;
-            const bool g1 = slab_cull_fused(cr, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), cull, e1);
-            const bool g2 = slab_cull_fused(cr, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), cull, e2);
-            const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
-            if (g1 && g2) {
-                const bool left_first = e1 <= e2;
-                if (stk.full()) { *sc.error_flag = PT_ERR_STACK; stk.clear(); ref = PT_REF_NONE; break; }
-                stk.push(left_first ? rref : lref);
-                ref = left_first ? lref : rref;
-            } else if (g1 || g2) {
-                ref = g1 ? lref : rref;
-            } else {
-                ref = PT_REF_NONE;
+        uint32_t next = PT_REF_NONE;                   // where this lane goes after its step (NONE: pop)
+        bool advance = false;
+        if (__popc(m_node) + PT_WF_NODE_BIAS >= __popc(m_tri)) {
+            // ---- node step: both child boxes and refs in one 64-byte record ----
+            if (mode == PT_WF_MODE_NODE) {
+                const float4* w = sc.wnodes_fast + 4 * (size_t)ref;
+                const float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
+                cnt.inner();
+                if (Cfg::COUNT) steps++;
+                float e1, e2;
+                const bool g1 = slab_cull_fused(cr, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), cull, e1);
+                const bool g2 = slab_cull_fused(cr, mk3(q1.z, q1.w, q2.x), mk3(q2.y, q2.z, q2.w), cull, e2);
+                const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+                advance = true;
+                if (g1 && g2) {
+                    const bool left_first = e1 <= e2;
+                    if (stk.full()) { *sc.error_flag = PT_ERR_STACK; stk.clear(); }
+                    else { stk.push(left_first ? rref : lref); next = left_first ? lref : rref; }
+                } else if (g1 || g2) {
+                    next = g1 ? lref : rref;
+                }
             }
-        }
-        if (ref != PT_REF_NONE) {
-            const uint32_t first = ref_index(ref), end = first + ref_count(ref);
-            for (uint32_t i = first; i < end; i++) {
+        } else {
+            // ---- triangle step: hitArray, one triangle per turn ----
+            if (mode == PT_WF_MODE_TRI) {
+                const uint32_t i = ti++;
                 const float4* g = sc.trigeo_fast + 3 * (size_t)i;
                 const float4 a = ldg4(g), bq = ldg4(g + 1), c = ldg4(g + 2);
                 cnt.tri();
                 if (Cfg::COUNT) steps++;
                 float tt; bool ins;
+                advance = ti == tend;
                 if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(bq.x, bq.y, bq.z), mk3(c.x, c.y, c.z), mk3(a.w, bq.w, c.w), res.t, tt, ins,
                                  !anyhit && res.tri >= 0)) {
                     cnt.cand();
                     const int2 meta = __ldg(sc.trimeta + i);
-                    if (meta.y != 1) {
+                    bool accept = true;
+                    if (meta.y != 1) {                // the reference never box-tests its root (P:342-343)
                         const float* nd = sc.nodes_raw + 12 * (size_t)meta.y;
                         float e;
                         r.inv = mk3(s_rcp(r.d.x), s_rcp(r.d.y), s_rcp(r.d.z));
-                        if (!(hit_aabb(r, raw3(nd + 6), raw3(nd + 9), e) > 0.0f)) continue;
+                        accept = hit_aabb(r, raw3(nd + 6), raw3(nd + 9), e) > 0.0f;
                     }
-                    if (!anyhit && tt == res.t) { tie = true; continue; }
-                    res.t = tt; res.tri = meta.x; res.inside = ins;
-                    if (anyhit) { stk.clear(); break; }
-                    cull = s_mul(tt, PT_CULL_SLACK);
+                    if (accept) {
+                        if (!anyhit && tt == res.t) {
+                            tie = true;
+                        } else {
+                            res.t = tt; res.tri = meta.x; res.inside = ins;
+                            if (anyhit) { stk.clear(); advance = true; }   // a shadow ray needs no more than this
+                            else cull = s_mul(tt, PT_CULL_SLACK);
+                        }
+                    }
                 }
             }
         }
-        // ---- pop, or this lane's ray is finished ----
-        if (state == 1) {
-            if (stk.empty()) { state = 2; ref = PT_REF_NONE; }
-            else ref = stk.pop();
+        // ---- where next: the child, or the next deferred subtree, or this ray is finished ----
+        if (advance) {
+            if (next == PT_REF_NONE) {
+                if (stk.empty()) mode = PT_WF_MODE_DONE;
+                else next = stk.pop();
+            }
+            if (mode != PT_WF_MODE_DONE) {
+                if (ref_count(next) == 0) { ref = next; mode = PT_WF_MODE_NODE; }
+                else { ti = ref_index(next); tend = ti + ref_count(next); mode = PT_WF_MODE_TRI; }
+            }
         }
     }
 }

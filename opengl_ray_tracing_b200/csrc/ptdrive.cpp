@@ -9,13 +9,19 @@
 //   M:659-709  display(): camera uniforms, frameCounter++, pass1/pass2/pass3 -> pt_set_camera, pt_render_spp, pt_readback_display
 // and, because there is no window, the image pass3 would show is written as a PNG (and the fp32 radiance as a PFM).
 //
+// --gpus N renders on N GPUs (one context and one host thread per GPU, the scene replicated): the image is split in diagonal
+// 8x4 tiles (--split tile: bit-identical to one GPU) or the frames are dealt round-robin (--split sample), and pt_combine
+// merges the N framebuffers into rank 0's image over NVLink.
+//
 //   ptdrive --variant 2 --icosphere 71 --size 1920x1080 --spp 256 --out image.png
+//   ptdrive --variant 2 --icosphere 224 --size 1920x1080 --spp 4096 --gpus 8 --out image.png
 //   ptdrive --variant 0 --obj model.obj --hdr sky.hdr --spp 64 --camera 10,25,2.5 --out image.png --pfm radiance.pfm
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/pt.h"
@@ -35,6 +41,8 @@ struct Options {
     bool basic = false;                 // --basic: BasicRayTracingWithC++/main.cpp instead (its own scene literal, 256x256)
     unsigned seed = 1;
     bool size_given = false;
+    int gpus = 1;                       // --gpus N: contexts on devices device .. device + N - 1
+    bool split_tiles = true;            // --split tile | sample
 };
 
 [[noreturn]] void die(const std::string& msg) {
@@ -45,7 +53,7 @@ struct Options {
 void usage() {
     std::puts("ptdrive [--variant 0|1|2] [--obj FILE | --icosphere N] [--hdr FILE | --synth-hdr WxH] [--size WxH] [--spp N]\n"
               "        [--spp-per-call K] [--camera UP,ROT,R] [--median] [--threads T] [--mode M] [--pipeline P] [--device D]\n"
-              "        [--max-bounce B] [--out image.png] [--pfm radiance.pfm]\n"
+              "        [--max-bounce B] [--gpus N [--split tile|sample]] [--out image.png] [--pfm radiance.pfm]\n"
               "ptdrive --basic [--size WxH] [--spp N] [--seed S] [--device D] [--out image.png]      (BasicRayTracingWithC++/main.cpp)");
 }
 
@@ -78,6 +86,8 @@ Options parse(int argc, char** argv) {
         else if (a == "--pipeline") o.pipeline = std::atoi(next());
         else if (a == "--device") o.device = std::atoi(next());
         else if (a == "--max-bounce") o.max_bounce = std::atoi(next());
+        else if (a == "--gpus") o.gpus = std::atoi(next());
+        else if (a == "--split") { const std::string v = next(); if (v != "tile" && v != "sample") die("--split wants tile or sample"); o.split_tiles = v == "tile"; }
         else if (a == "--out") o.out = next();
         else if (a == "--pfm") o.pfm = next();
         else if (a == "-h" || a == "--help") { usage(); std::exit(0); }
@@ -85,6 +95,7 @@ Options parse(int argc, char** argv) {
     }
     if (o.variant < 0 || o.variant > 2) die("--variant must be 0, 1 or 2");
     if (o.spp == 0 || o.per_call == 0) die("--spp and --spp-per-call must be positive");
+    if (o.gpus < 1 || o.gpus > 16) die("--gpus must be 1 .. 16");
     return o;
 }
 
@@ -158,6 +169,62 @@ int run_basic(const Options& o) {
     return 0;
 }
 
+// display() on N GPUs: one host thread and one context per GPU; rank r renders its share, pt_combine merges.
+void run_multi_gpu(const Options& o, pts_scene* sc, int nTriangles, int nNodes, const float* hdr, const float* cache, int hw, int hh,
+                   const float eye[3], const float cam[16]) {
+    const int N = o.gpus;
+    unsigned char id[PT_COMM_ID_BYTES];
+    ptcheck(pt_comm_get_unique_id(id, sizeof id), "pt_comm_get_unique_id");
+    std::vector<unsigned char> rgba8((size_t)o.width * o.height * 4);
+    std::vector<float> rgba(o.pfm.empty() ? 0 : (size_t)o.width * o.height * 4);
+    std::vector<PtStats> stats((size_t)N);
+    std::vector<double> wall((size_t)N, 0.0);
+    std::vector<int> peer((size_t)N, 0);
+    auto worker = [&](int r) {
+        // a rank that fails ends the process at once: the other ranks would wait for it in the next collective for ever
+        auto check = [&](int rc, const char* what) { if (rc != PT_OK) die("rank " + std::to_string(r) + ": " + what + ": " + pt_last_error()); return true; };
+        PtConfig cfg = {o.variant, o.width, o.height, o.max_bounce, o.device + r, o.mode, o.pipeline};
+        pt_ctx* pt = nullptr;
+        if (!check(pt_create(&cfg, &pt), "pt_create")) return;
+        bool ok = check(pt_upload_scene(pt, pts_triangles_encoded(sc), nTriangles, pts_nodes_encoded(sc), nNodes, hdr, cache, hw, hh), "pt_upload_scene") &&
+                  check(pt_comm_init(pt, N, r, id, sizeof id), "pt_comm_init") && check(pt_set_camera(pt, eye, cam), "pt_set_camera");
+        if (ok && o.split_tiles) ok = check(pt_set_tile_interleave(pt, N, r), "pt_set_tile_interleave");
+        if (ok) pt_comm_info(pt, nullptr, nullptr, &peer[(size_t)r]);
+        const double t0 = now();
+        unsigned done = 0;
+        while (ok && done < o.spp) {                                     // the display() loop, this rank's share of every call
+            const unsigned n = o.spp - done < o.per_call ? o.spp - done : o.per_call;
+            if (o.split_tiles) {
+                ok = check(pt_render_spp(pt, done, n), "pt_render_spp");
+            } else {
+                const unsigned mine = n > (unsigned)r ? (n - (unsigned)r + (unsigned)N - 1) / (unsigned)N : 0;   // frames done + r, done + r + N, ...
+                if (mine) ok = check(pt_render_frames(pt, done + (unsigned)r, mine, (unsigned)N, PT_ACC_SUM), "pt_render_frames");
+            }
+            done += n;
+        }
+        const int flags = (o.split_tiles ? PT_COMBINE_DISJOINT : PT_COMBINE_SUM) | PT_COMBINE_DISPLAY;
+        if (ok) ok = check(pt_combine(pt, flags, o.spp, r == 0 && !rgba.empty() ? rgba.data() : nullptr, r == 0 ? rgba8.data() : nullptr), "pt_combine");
+        if (ok) ok = check(pt_synchronize(pt), "pt_synchronize");
+        wall[(size_t)r] = now() - t0;
+        if (ok) check(pt_get_stats(pt, &stats[(size_t)r]), "pt_get_stats");
+        pt_destroy(pt);
+    };
+    std::vector<std::thread> th;
+    for (int r = 0; r < N; r++) th.emplace_back(worker, r);
+    for (auto& t : th) t.join();
+    double ms = 0.0, w = 0.0;
+    unsigned long long rays = 0;
+    for (int r = 0; r < N; r++) { ms = stats[(size_t)r].render_ms > ms ? stats[(size_t)r].render_ms : ms; w = wall[(size_t)r] > w ? wall[(size_t)r] : w; rays += stats[(size_t)r].rays; }
+    std::printf("rendered %u spp at %dx%d on %d GPUs (%s split, combine over %s): %.2f ms on the slowest device (%.2f ms wall), %.1f Mrays/s\n", o.spp, o.width,
+                o.height, N, o.split_tiles ? "tile" : "sample", peer[0] ? "NVLink peer memory" : "ncclReduce", ms, w * 1e3, (double)rays / (ms * 1e3));
+    ptscheck(pts_write_png(o.out.c_str(), rgba8.data(), o.width, o.height, 4), "pts_write_png");
+    std::printf("wrote %s\n", o.out.c_str());
+    if (!o.pfm.empty()) {
+        ptscheck(pts_write_pfm(o.pfm.c_str(), rgba.data(), o.width, o.height), "pts_write_pfm");
+        std::printf("wrote %s\n", o.pfm.c_str());
+    }
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -195,18 +262,25 @@ int main(int argc, char** argv) {
     }
     std::printf("environment: %dx%d%s (%.2f s)\n", hw, hh, cache.empty() ? "" : " + hdrCache", now() - t0);
 
+    float eye[3], cam[16];
+    pts_camera(o.up, o.rot, o.r, eye, cam);
+    const float* hdr_cache = cache.empty() ? nullptr : cache.data();
+    if (o.gpus > 1) {
+        run_multi_gpu(o, sc, nTriangles, nNodes, hdr_data, hdr_cache, hw, hh, eye, cam);
+        if (hdr) pts_free(hdr);
+        pts_scene_destroy(sc);
+        return 0;
+    }
+
     // ---- context + upload (M:746-751, M:823-873) ----
     PtConfig cfg = {o.variant, o.width, o.height, o.max_bounce, o.device, o.mode, o.pipeline};
     pt_ctx* pt = nullptr;
     ptcheck(pt_create(&cfg, &pt), "pt_create");
     t0 = now();
-    ptcheck(pt_upload_scene(pt, pts_triangles_encoded(sc), nTriangles, pts_nodes_encoded(sc), nNodes, hdr_data,
-                            cache.empty() ? nullptr : cache.data(), hw, hh), "pt_upload_scene");
+    ptcheck(pt_upload_scene(pt, pts_triangles_encoded(sc), nTriangles, pts_nodes_encoded(sc), nNodes, hdr_data, hdr_cache, hw, hh), "pt_upload_scene");
     std::printf("upload: %.2f s\n", now() - t0);
 
     // ---- display() loop (M:659-709) ----
-    float eye[3], cam[16];
-    pts_camera(o.up, o.rot, o.r, eye, cam);
     ptcheck(pt_set_camera(pt, eye, cam), "pt_set_camera");
     t0 = now();
     unsigned frameCounter = 0;

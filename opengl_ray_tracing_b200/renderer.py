@@ -22,7 +22,7 @@ MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE, MODE_PARITY_FAST, MODE_FAST_COUNT 
 DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 
 ACC_MEAN, ACC_SUM = 0, 1
-COMBINE_SUM, COMBINE_DISJOINT = 0, 1
+COMBINE_SUM, COMBINE_DISJOINT, COMBINE_DISPLAY = 0, 1, 4
 COMM_ID_BYTES = 128
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
@@ -222,19 +222,20 @@ class PathTracer:
         _check(lib().pt_comm_info(self._h, C.byref(w), C.byref(r), C.byref(p)), "pt_comm_info")
         return {"world": w.value, "rank": r.value, "peer_memory": bool(p.value)}
 
-    def combine(self, kind, total_frames=0, out_ptr=None, display_ptr=None):
-        """Collective: all ranks' framebuffers -> one image on rank 0 (pt_combine).  out_ptr / display_ptr: host addresses or None."""
-        _check(lib().pt_combine(self._h, kind, total_frames, out_ptr, display_ptr), "pt_combine")
+    def combine(self, flags, total_frames=0, out_ptr=None, display_ptr=None):
+        """Collective: all ranks' framebuffers -> one image on rank 0 (pt_combine).  flags = COMBINE_SUM | COMBINE_DISJOINT
+        [| COMBINE_DISPLAY], the same on every rank; out_ptr / display_ptr: host addresses on rank 0, or None."""
+        _check(lib().pt_combine(self._h, flags, total_frames, out_ptr, display_ptr), "pt_combine")
 
     def combine_readback(self, kind, total_frames=0, display=False):
         """Rank 0: returns the combined float32 [H, W, 4] image (and the uint8 display image); other ranks: None."""
-        info = self.comm_info()
-        if info["rank"] != 0:
-            self.combine(kind, total_frames)
+        flags = kind | (COMBINE_DISPLAY if display else 0)
+        if self.comm_info()["rank"] != 0:
+            self.combine(flags, total_frames)
             return None
         img = np.empty((self.height, self.width, 4), np.float32)
         disp = np.empty((self.height, self.width, 4), np.uint8) if display else None
-        self.combine(kind, total_frames, img.ctypes.data, disp.ctypes.data if display else None)
+        self.combine(flags, total_frames, img.ctypes.data, disp.ctypes.data if display else None)
         return (img, disp) if display else img
 
     def stats(self) -> dict:

@@ -50,7 +50,7 @@ def newer(target, *sources):
 _FLOAT_LIT = re.compile(r"(?<![\w.])((?:\d+\.\d*|\.\d+)(?:[eE][-+]?\d+)?|\d+[eE][-+]?\d+)(?![\w.])")
 
 
-def shader_to_cpp(src: str) -> str:
+def shader_to_cpp(src: str, pass1: bool = True) -> str:
     src = src.replace("\r\n", "\n")
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)              # block comments
     src = re.sub(r"//[^\n]*", "", src)                            # line comments (GBK bytes, may end in '\')
@@ -59,6 +59,8 @@ def shader_to_cpp(src: str) -> str:
     for sw in ("xyz", "rgb", "rg", "xy"):                         # multi-component swizzles -> methods
         src = re.sub(r"\.%s\b(?!\()" % sw, ".%s()" % sw, src)
     src = re.sub(r"\binout\s+(\w+)\s+", r"\1& ", src)            # inout T x -> T& x
+    if not pass1:
+        return src
     src = src.replace("const uint V[8*32] = {", "static constexpr uint V[8*32] = {")
     # hitBVH's `int stack[256]` (pass1.fsh:340) is overrun by the reference's own SAH trees on large meshes (chains
     # thousands of nodes deep); on a GPU that is undefined behaviour, on the CPU it would smash the C++ stack.
@@ -94,6 +96,21 @@ def build_shaders():
             if math == "ptmath":
                 cmd.append("-DREF_MATH_PTMATH")
             run(cmd + [wrap, "-o", so])
+
+
+def build_pass3():
+    """The display pass (toneMapping, pass3.fsh:14-24) compiled from the reference's text: oracle of pt_readback_display."""
+    path = os.path.join(REF, IS_DIR, "shaders", "pass3.fsh")
+    wrap = os.path.join(HERE, "ref_pass3_wrap.cpp")
+    inc = os.path.join(OUT, "pass3.inc")
+    so = os.path.join(OUT, "libref_pass3.so")
+    if newer(so, path, wrap, os.path.join(HERE, "glsl_compat.h"), __file__):
+        return
+    with open(path, "r", encoding="latin-1") as f:
+        text = shader_to_cpp(f.read(), pass1=False)
+    with open(inc, "w", encoding="latin-1") as f:
+        f.write(text)
+    run(["g++", *CXXFLAGS, "-shared", "-I", HERE, "-I", INC, '-DREF_PASS3_INC="%s"' % inc, wrap, "-o", so])
 
 
 # ---------------------------------------------------------------- host functions of IS/main.cpp
@@ -205,6 +222,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     build_host()
     build_shaders()
+    build_pass3()
     if "--no-basic" not in sys.argv:
         build_basic()
         build_basic_det()

@@ -94,6 +94,12 @@ def ref_shader_available(variant, math="ptmath"):
     return os.path.exists(os.path.join(REF_DIR, "libref_shader_%s_%s.so" % (REF_SHADER[variant], math)))
 
 
+def ref_shader_threads(variant, math="ptmath"):
+    """OpenMP threads the compiled reference shader runs on."""
+    L = C.CDLL(os.path.join(REF_DIR, "libref_shader_%s_%s.so" % (REF_SHADER[variant], math)))
+    return int(L.ref_shader_num_threads()) if hasattr(L, "ref_shader_num_threads") else num_threads()
+
+
 def ref_shader_render(variant, tris, nodes, hdr, hdrCache, width, height, eye, cam, first_frame, n_frames, accum=None,
                       math="ptmath", region=None):
     L = C.CDLL(os.path.join(REF_DIR, "libref_shader_%s_%s.so" % (REF_SHADER[variant], math)))
