@@ -58,6 +58,13 @@ extern "C" {
                                      in HBM (DESIGN.md "Pipelines"); not available for PT_MODE_PARITY_REF */
 #define PT_PIPELINE_PERSISTENT 2  /* persistent warps claim (8x4 tile, frame) items frame-major and accumulate in frame order */
 
+/* how variant 2 turns two random numbers into an environment light sample (SampleHdr, P:573-585) */
+#define PT_ENV_TABLE       0   /* the reference's: NEAREST lookup in the precomputed hdrCache table (calculateHdrCache, M:555-652) */
+#define PT_ENV_CDF_SEARCH  1   /* SURVEY.md 8f.3, opt-in, NOT the reference's image: binary search of the marginal / conditional CDFs
+                                  (the same fp32 tables calculateHdrCache inverts) per sample, on the continuous random numbers
+                                  instead of the table's W x H grid of them; needs no hdrCache (33.6 MB) and no light table (67 MB
+                                  at 2048x1024).  Variant 2, persistent pipeline, PT_MODE_FAST or PT_MODE_PARITY_FAST. */
+
 typedef struct PtConfig {
     int variant;        /* PT_VARIANT_* */
     int width, height;  /* framebuffer size; pass1.width/height M:82-83, uniforms M:871-872 */
@@ -65,6 +72,7 @@ typedef struct PtConfig {
     int device;         /* CUDA device ordinal */
     int mode;           /* PT_MODE_* */
     int pipeline;       /* PT_PIPELINE_* */
+    int env_sampler;    /* PT_ENV_* (0 = the reference's) */
 } PtConfig;
 
 typedef struct PtStats {

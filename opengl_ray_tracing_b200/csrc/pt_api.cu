@@ -35,6 +35,9 @@ struct FastTree {
 };
 void build_fast_tree(const float* tris_raw, int nTriangles, const float* nodes_raw, int nNodes, FastTree& out, int threads);
 cudaError_t hdr_cache_device(const float* d_rgb, int W, int H, float4* d_cache4, float* d_cache3, cudaStream_t st);   // pt_hdrcache.cu
+cudaError_t hdr_cdf_device(const float* d_rgb, int W, int H, float** pdf_out, float** cdf_x_out, float** cdf_yT_out, cudaStream_t st);
+cudaError_t launch_persistent_fast_cdf(const RenderParams& p, int grid, cudaStream_t stream);
+cudaError_t launch_persistent_parity_cdf(const RenderParams& p, int grid, cudaStream_t stream);
 cudaError_t launch_fast(const RenderParams& p, int variant, bool count, cudaStream_t stream);
 cudaError_t build_light_table_parity(const DevScene& sc, float4* tab, cudaStream_t stream);   // pt_kernels_parity.cu
 cudaError_t derive_materials_parity(float4* materials, int n, cudaStream_t stream);
@@ -98,16 +101,16 @@ __global__ void k_build_tris(const float* __restrict__ tris, int nTriangles, con
     shade[3 * (size_t)i + 2] = make_float4(t[15], t[16], t[17], 0.f);
 }
 
-// trigeo in the traversal tree's order + (uploaded index, reference leaf node) per re-ordered triangle
+// trigeo in the traversal tree's order + (uploaded index, reference leaf node) per re-ordered triangle: 64-byte records
 __global__ void k_gather_tris(const float4* __restrict__ geo, const int* __restrict__ order, const int* __restrict__ leaf_node,
-                              int nTriangles, float4* __restrict__ geo_fast, int2* __restrict__ meta) {
+                              int nTriangles, float4* __restrict__ geo_fast) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nTriangles) return;
     const int o = order[i];
-    geo_fast[3 * (size_t)i] = geo[3 * (size_t)o];
-    geo_fast[3 * (size_t)i + 1] = geo[3 * (size_t)o + 1];
-    geo_fast[3 * (size_t)i + 2] = geo[3 * (size_t)o + 2];
-    meta[i] = make_int2(o, leaf_node[i]);
+    geo_fast[4 * (size_t)i] = geo[3 * (size_t)o];
+    geo_fast[4 * (size_t)i + 1] = geo[3 * (size_t)o + 1];
+    geo_fast[4 * (size_t)i + 2] = geo[3 * (size_t)o + 2];
+    geo_fast[4 * (size_t)i + 3] = make_float4(__int_as_float(o), __int_as_float(leaf_node[i]), 0.f, 0.f);
 }
 
 __global__ void k_rgb_to_float4(const float* __restrict__ src, size_t n, float4* __restrict__ dst) {
@@ -164,36 +167,59 @@ cudaError_t create_events(pt_ctx* c) {
 }
 
 void free_scene(pt_ctx* c) {
-    cudaFree(c->trigeo_fast); cudaFree(c->trimeta);
-    c->trigeo_fast = nullptr; c->trimeta = nullptr;
+    cudaFree(c->trigeo_fast);
+    c->trigeo_fast = nullptr;
     cudaFree(c->tris_raw); cudaFree(c->nodes_raw); cudaFree(c->wnodes); cudaFree(c->wnodes_fast); cudaFree(c->trigeo); cudaFree(c->trishade);
     cudaFree(c->materials); cudaFree(c->hdr4); cudaFree(c->cache4); cudaFree(c->light_tab);
+    cudaFree(c->env_pdf); cudaFree(c->env_cdf_x); cudaFree(c->env_cdf_y);
+    c->env_pdf = c->env_cdf_x = c->env_cdf_y = nullptr;
     c->tris_raw = c->nodes_raw = nullptr;
     c->wnodes = c->wnodes_fast = c->trigeo = c->trishade = c->materials = c->hdr4 = c->cache4 = c->light_tab = nullptr;
     c->has_scene = false;
 }
 
-// Host-side validation of the reference-layout tree: every index in range, children after their parent
-// (the builders emit pre-order), both children present on inner nodes.  Returns the tree depth or < 0.
-int validate_tree(const float* nodes, int nNodes, int nTriangles, std::string& why) {
+// Host-side validation of the reference-layout tree: every index in range, children after their parent (the builders emit
+// pre-order), both children present on inner nodes, every node reachable, and the leaves' ranges a partition of the
+// triangles.  `nested` reports whether every child box lies inside its parent's (the root's box aside: the reference never
+// tests it, P:342-343) — the premise of the production traversal's "a hit on the leaf's box implies one on all its
+// ancestors'" (pt_trace.cuh trace_fast).  Returns the tree depth or < 0.
+int validate_tree(const float* nodes, int nNodes, int nTriangles, std::string& why, bool& nested) {
+    nested = true;
     if (nNodes < 2) { why = "need the dummy node 0 and a root node 1"; return -1; }
     std::vector<int> depth((size_t)nNodes, 0);
+    std::vector<unsigned char> owned((size_t)nTriangles, 0);
     depth[1] = 1;
     int max_depth = 1;
+    long long covered = 0;
     for (int i = 1; i < nNodes; i++) {
         const float* nd = nodes + 12 * (size_t)i;
         int l = (int)nd[0], r = (int)nd[1], n = (int)nd[3], index = (int)nd[4];
         if ((float)l != nd[0] || (float)r != nd[1] || (float)n != nd[3] || (float)index != nd[4]) { why = "non-integer index in node " + std::to_string(i); return -1; }
+        if (n < 0) { why = "negative triangle count in node " + std::to_string(i); return -1; }
+        if (depth[i] == 0) { why = "node " + std::to_string(i) + " is unreachable"; return -1; }
         if (n > 0) {
             if (index < 0 || (long long)index + n > nTriangles) { why = "leaf range out of bounds in node " + std::to_string(i); return -1; }
             if (n > 255) { why = "leaf with more than 255 triangles (node " + std::to_string(i) + ")"; return -1; }
+            for (int k = 0; k < n; k++) {
+                if (owned[(size_t)index + k]) { why = "triangle " + std::to_string(index + k) + " belongs to two leaves (node " + std::to_string(i) + ")"; return -1; }
+                owned[(size_t)index + k] = 1;
+            }
+            covered += n;
         } else {
-            if (l <= i || r <= i || l >= nNodes || r >= nNodes) { why = "child index out of order/bounds in node " + std::to_string(i); return -1; }
-            if (depth[i] == 0) { why = "node " + std::to_string(i) + " is unreachable"; return -1; }
+            if (l <= i || r <= i || l >= nNodes || r >= nNodes || l == r) { why = "child index out of order/bounds in node " + std::to_string(i); return -1; }
+            if (depth[l] || depth[r]) { why = "node " + std::to_string(depth[l] ? l : r) + " has two parents"; return -1; }
             depth[l] = depth[r] = depth[i] + 1;
             if (depth[i] + 1 > max_depth) max_depth = depth[i] + 1;
+            if (i != 1) {
+                for (int c : {l, r}) {
+                    const float* cd = nodes + 12 * (size_t)c;
+                    for (int a = 0; a < 3; a++)
+                        if (!(cd[6 + a] >= nd[6 + a]) || !(cd[9 + a] <= nd[9 + a])) nested = false;
+                }
+            }
         }
     }
+    if (covered != nTriangles) { why = std::to_string(nTriangles - covered) + " triangles belong to no leaf"; return -1; }
     return max_depth;
 }
 
@@ -270,6 +296,10 @@ int pt_create(const PtConfig* cfg, pt_ctx** out) {
         return fail(PT_EINVAL, "pt_create: PT_MODE_PARITY_REF (the reference's own layout and traversal) runs as a megakernel only");
     if (cfg->pipeline == PT_PIPELINE_WAVEFRONT && mb > PT_WF_MAX_BOUNCE)
         return fail(PT_EINVAL, "pt_create: the wavefront pipeline supports max_bounce <= 8");
+    if (cfg->env_sampler != PT_ENV_TABLE && cfg->env_sampler != PT_ENV_CDF_SEARCH) return fail(PT_EINVAL, "pt_create: env_sampler must be one of PT_ENV_*");
+    if (cfg->env_sampler == PT_ENV_CDF_SEARCH &&
+        (cfg->variant != PT_VARIANT_DISNEY_IS_MIS || cfg->pipeline != PT_PIPELINE_PERSISTENT || (cfg->mode != PT_MODE_FAST && cfg->mode != PT_MODE_PARITY_FAST)))
+        return fail(PT_EINVAL, "pt_create: PT_ENV_CDF_SEARCH needs variant 2, the persistent pipeline and PT_MODE_FAST or PT_MODE_PARITY_FAST");
     int ndev = 0;
     CK(cudaGetDeviceCount(&ndev));
     if (cfg->device < 0 || cfg->device >= ndev) return fail(PT_EINVAL, "pt_create: no such CUDA device");
@@ -324,8 +354,13 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     if (nTriangles >= (1 << 24) || nNodes >= (1 << 24))
         return fail(PT_ERANGE, "pt_upload_scene: index not exact in the reference's float encoding (>= 2^24)");
     std::string why;
-    int depth = validate_tree(nodes, nNodes, nTriangles, why);
+    bool nested = true;
+    int depth = validate_tree(nodes, nNodes, nTriangles, why, nested);
     if (depth < 0) return fail(PT_EFORMAT, "pt_upload_scene: " + why);
+    if (!nested && c->cfg.mode != PT_MODE_PARITY_REF && c->cfg.mode != PT_MODE_PARITY_WIDE)
+        return fail(PT_EFORMAT, "pt_upload_scene: a child box is not inside its parent's; the production traversal (PT_MODE_FAST, "
+                                "PT_MODE_PARITY_FAST) needs nested boxes, as buildBVH / buildBVHwithSAH produce them — "
+                                "PT_MODE_PARITY_REF and PT_MODE_PARITY_WIDE follow the array as it is");
     // depth > 256 is accepted: the reference's stack[256] (pass1.fsh:340) only overflows if a RAY defers more than
     // 256 subtrees at once; the kernels detect an overflow of their own stacks at run time (PT_MODE_PARITY_REF: 256
     // entries like the reference; the wide/production traversals: PT_STACK = 128 deferred subtrees on trees of depth
@@ -422,9 +457,8 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         CKU(cudaMalloc(&d_leaf, (size_t)nTriangles * sizeof(int)));
         CKU(cudaMemcpyAsync(d_order, ft.order.data(), (size_t)nTriangles * sizeof(int), cudaMemcpyHostToDevice, st));
         CKU(cudaMemcpyAsync(d_leaf, ft.leaf_node.data(), (size_t)nTriangles * sizeof(int), cudaMemcpyHostToDevice, st));
-        CKU(cudaMalloc(&c->trigeo_fast, (size_t)nTriangles * 3 * sizeof(float4)));
-        CKU(cudaMalloc(&c->trimeta, (size_t)nTriangles * sizeof(int2)));
-        k_gather_tris<<<(nTriangles + 255) / 256, 256, 0, st>>>(c->trigeo, d_order, d_leaf, nTriangles, c->trigeo_fast, c->trimeta);
+        CKU(cudaMalloc(&c->trigeo_fast, (size_t)nTriangles * 4 * sizeof(float4)));
+        k_gather_tris<<<(nTriangles + 255) / 256, 256, 0, st>>>(c->trigeo, d_order, d_leaf, nTriangles, c->trigeo_fast);
         CKU(cudaGetLastError());
         CKU(cudaStreamSynchronize(st));               // ft goes out of scope
     }
@@ -440,7 +474,11 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     CKU(cudaMemcpyAsync(d_tmp, hdr, ntex * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
     k_rgb_to_float4<<<(unsigned)((ntex + 255) / 256), 256, 0, st>>>(d_tmp, ntex, c->hdr4);
     CKU(cudaGetLastError());
-    if (hdrCache) {
+    if (c->cfg.env_sampler == PT_ENV_CDF_SEARCH) {
+        // no table at all: the marginal / conditional CDFs calculateHdrCache inverts, searched per sample (pt_shade.cuh SampleHdr)
+        CKU(pt::hdr_cdf_device(d_tmp, hdrW, hdrH, &c->env_pdf, &c->env_cdf_x, &c->env_cdf_y, st));
+        cache_launches = 6;
+    } else if (hdrCache) {
         CKU(cudaMalloc(&c->cache4, ntex * sizeof(float4)));
         CKU(cudaStreamSynchronize(st));
         CKU(cudaMemcpyAsync(d_tmp, hdrCache, ntex * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
@@ -456,10 +494,11 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     {
         pt::DevScene& s = c->sc;
         s.tris_raw = c->tris_raw; s.nodes_raw = c->nodes_raw; s.wnodes = c->wnodes; s.wnodes_fast = c->wnodes_fast; s.trigeo = c->trigeo;
-        s.trigeo_fast = c->trigeo_fast; s.trimeta = c->trimeta;
+        s.trigeo_fast = c->trigeo_fast;
         s.root_fast = root_fast; c->fast_depth = fast_depth; c->n_fast_inner = nFastInner;
         s.trishade = c->trishade; s.materials = c->materials; s.hdr4 = c->hdr4; s.cache4 = c->cache4;
-        s.nTriangles = nTriangles; s.nNodes = nNodes; s.nInner = nInner; s.nMaterials = nMaterials;
+        s.env_pdf = c->env_pdf; s.env_cdf_x = c->env_cdf_x; s.env_cdf_y = c->env_cdf_y;
+        s.nTriangles = nTriangles; s.nNodes = nNodes; s.nInner = nInner; s.nMaterials = nMaterials; s.nFastInner = nFastInner;
         s.hdrW = hdrW; s.hdrH = hdrH; s.stack_depth = depth; s.error_flag = c->error_flag; s.ray_histogram = c->ray_counter + 8;
         // root = node 1: a leaf when the whole scene fits one leaf, else wide node 0
         int rn = (int)nodes[12 + 3], rindex = (int)nodes[12 + 4];
@@ -557,6 +596,10 @@ static int collect_timing(pt_ctx* c, bool wait = true) {
     if (!wait) return PT_OK;
     int flag = 0;
     CK(cudaMemcpy(&flag, c->error_flag, sizeof flag, cudaMemcpyDeviceToHost));
+    if (flag == PT_ERR_BOUNDS) {
+        CK(cudaMemset(c->error_flag, 0, sizeof flag));
+        return fail(PT_ERANGE, "render kernel: an index left its array (PT_DEBUG_BOUNDS build) - image is invalid");
+    }
     if (flag) {
         CK(cudaMemset(c->error_flag, 0, sizeof flag));
         return fail(PT_ERANGE, "render kernel: traversal stack overflow (a ray deferred more subtrees than the traversal stack holds: "
@@ -643,8 +686,11 @@ int pt_render_frames(pt_ctx* c, unsigned first_frame, unsigned n_frames, unsigne
                      : pt::launch_wavefront_parity(p, c->cfg.variant, c->cfg.mode, sms, c->stream, &wstats);
     } else if (persistent) {
         const int grid = c->num_sms > 0 ? c->num_sms : 148;   // the launcher multiplies by the kernel's CTAs per SM
-        e = fastmode ? pt::launch_persistent_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
-                     : pt::launch_persistent_parity(p, c->cfg.variant, c->cfg.mode, grid, c->stream);
+        if (c->cfg.env_sampler == PT_ENV_CDF_SEARCH)
+            e = fastmode ? pt::launch_persistent_fast_cdf(p, grid, c->stream) : pt::launch_persistent_parity_cdf(p, grid, c->stream);
+        else
+            e = fastmode ? pt::launch_persistent_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, grid, c->stream)
+                         : pt::launch_persistent_parity(p, c->cfg.variant, c->cfg.mode, grid, c->stream);
     } else {
         e = fastmode ? pt::launch_fast(p, c->cfg.variant, c->cfg.mode == PT_MODE_FAST_COUNT, c->stream)
                      : pt::launch_parity(p, c->cfg.variant, c->cfg.mode, c->stream);

@@ -59,6 +59,20 @@ __device__ __forceinline__ V3 s_point(V3 S, V3 d, float t) {
 // ---- read-only loads: ld.global.nc (the scene is immutable while a render kernel runs) ----------
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 __device__ __forceinline__ float ldg1(const float* p) { return __ldg(p); }
+// 32 bytes in ONE load (sm_100: LDG.E.256): a 64-byte traversal record is two L1 tag look-ups instead of four.  With the
+// lanes of a warp at 32 different records the L1's tag stage, not bandwidth, is what a node step waits for
+// (profiles/r02_wavefront.md: l1tex throughput 91 % of peak in the traversal-only kernel).  p must be 32-byte aligned.
+#ifndef PT_LD256
+#define PT_LD256 1
+#endif
+__device__ __forceinline__ void ldg8(const float4* p, float4& a, float4& b) {
+#if PT_LD256
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+#else
+    a = __ldg(p); b = __ldg(p + 1);
+#endif
+}
 
 // ---- packed child reference of the wide BVH ----------------------------------------------------
 // bits 0..23 = index (inner: wide-node index; leaf: first triangle), bits 24..31 = triangle count
@@ -76,15 +90,19 @@ struct DevScene {
     // traversal layout built on the device at upload
     const float4* wnodes;       // nInner x 4 float4 (64 B): child boxes + packed child refs, REFERENCE topology
     const float4* wnodes_fast;  // same record format, binned-SAH topology over the triangles (pt_build.cpp), padded boxes
-    const float4* trigeo_fast;  // trigeo re-ordered so that a leaf of wnodes_fast is a contiguous range
-    const int2* trimeta;        // per re-ordered triangle: (uploaded triangle index, reference leaf node holding it)
+    const float4* trigeo_fast;  // nTriangles x 4 float4 (64 B), in the order of wnodes_fast's leaves: trigeo's three + (uploaded triangle
+                                // index, reference leaf node holding it, -, -) as int bits: one 64-byte record per triangle test
     const float4* trigeo;       // nTriangles x 3 float4 (48 B): (p1,N.x) (p2,N.y) (p3,N.z), N = unit face normal
     const float4* trishade;     // nTriangles x 3 float4 (48 B): (n1, matId) (n2, -) (n3, -)
     const float4* materials;    // nMaterials x 8 float4 (128 B): the 16 parameters, then 16 values derived from them (pt_shade.cuh MaterialD)
     const float4* hdr4;         // hdrH x hdrW float4 (rgb, 0)
     const float4* cache4;       // hdrH x hdrW float4 (x/w, y/h, pdf, 0) or null
     const float4* light_tab;    // hdrH x hdrW x 2 float4: what a light sample through each cache texel evaluates to (pt_shade.cuh) or null
-    int nTriangles, nNodes, nInner, nMaterials;
+    // PT_ENV_CDF_SEARCH (cache4 and light_tab are null then): calculateHdrCache's intermediates, searched per sample
+    const float* env_cdf_x;     // hdrW: marginal CDF over the columns
+    const float* env_cdf_y;     // hdrW x hdrH: conditional CDF of every column, contiguous per column
+    const float* env_pdf;       // hdrH x hdrW: pdf per texel (the table's B channel)
+    int nTriangles, nNodes, nInner, nMaterials, nFastInner;
     int hdrW, hdrH;
     uint32_t root_ref, root_fast;
     int stack_depth;            // depth of the tree = worst-case traversal stack
@@ -92,6 +110,22 @@ struct DevScene {
     int* error_flag;            // set to PT_ERR_* by a kernel that had to give up (checked at the next sync)
 };
 #define PT_ERR_STACK 1          // traversal stack overflow: more deferred subtrees than PT_STACK (pt_trace.cuh: 128; trace_ref keeps the reference's stack[256], P:340)
+
+// PT_DEBUG_BOUNDS build (tools/build_variant.py dbg -DPT_DEBUG_BOUNDS=1): every index the kernels form from scene or queue data
+// is range-checked before use; a violation raises PT_ERR_BOUNDS (reported as PT_ERANGE at the next synchronising call) and
+// the access is redirected to element 0.  compute-sanitizer is closed on the GPU pool this was developed on, so the GPU test
+// suite is run once against this build instead (profiles/r02_bounds_check.md).
+#define PT_ERR_BOUNDS 2
+#if defined(PT_DEBUG_BOUNDS) && PT_DEBUG_BOUNDS
+#define PT_IDX(sc, i, n) pt::checked_index((sc).error_flag, (size_t)(i), (size_t)(n))
+__device__ __forceinline__ size_t checked_index(int* flag, size_t i, size_t n) {
+    if (i < n) return i;
+    *flag = PT_ERR_BOUNDS;
+    return 0;
+}
+#else
+#define PT_IDX(sc, i, n) (i)
+#endif
 
 // Path state of the wavefront pipeline (pt_wavefront.cuh), struct-of-arrays in HBM.
 //   per PATH (compact ids handed out by wf_head to the paths that survive their primary ray; `pcap` of them)

@@ -99,7 +99,51 @@ __global__ void k_lookup(const float* __restrict__ pdf, const float* __restrict_
     else { out[3 * idx] = ox; out[3 * idx + 1] = oy; out[3 * idx + 2] = op; }
 }
 
+// cdf_y [i][j] (coalesced for k_columns) -> [j][i]: the column a binary search walks is contiguous
+__global__ void k_transpose(const float* __restrict__ in, int W, int H, float* __restrict__ out) {
+    __shared__ float tile[32][33];
+    const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int i = i0 + r, j = j0 + threadIdx.x;
+        if (i < H && j < W) tile[r][threadIdx.x] = in[(size_t)i * W + j];
+    }
+    __syncthreads();
+    for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+        const int j = j0 + r, i = i0 + threadIdx.x;
+        if (i < H && j < W) out[(size_t)j * H + i] = tile[threadIdx.x][r];
+    }
+}
+
 }  // namespace
+
+// The CDF-search environment sampler's tables (PtConfig.env_sampler = PT_ENV_CDF_SEARCH): the intermediates of
+// calculateHdrCache, M:555-609, by the same kernels as the table build below — pdf [H][W], the marginal CDF over the
+// columns cdf_x [W], the conditional CDFs column by column cdf_yT [W][H].  The caller owns the three allocations.
+cudaError_t hdr_cdf_device(const float* d_rgb, int W, int H, float** pdf_out, float** cdf_x_out, float** cdf_yT_out, cudaStream_t st) {
+    const size_t n = (size_t)W * H;
+    float *pdf = nullptr, *cdf_y = nullptr, *cdf_yT = nullptr, *small = nullptr, *cdf_x = nullptr;
+    cudaError_t e = cudaMalloc(&pdf, n * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&cdf_y, n * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&cdf_yT, n * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&small, ((size_t)W + 1) * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&cdf_x, (size_t)W * sizeof(float));
+    if (e == cudaSuccess) {
+        float *pdf_x = small, *lum_sum = small + W;
+        const unsigned blocks = (unsigned)((n + 255) / 256);
+        k_luminance<<<blocks, 256, 0, st>>>(d_rgb, n, pdf);
+        k_sequential_sum<<<1, 1024, 0, st>>>(pdf, n, lum_sum);
+        k_normalise<<<blocks, 256, 0, st>>>(pdf, n, lum_sum);
+        k_columns<<<(W + 127) / 128, 128, 0, st>>>(pdf, W, H, pdf_x, cdf_y);
+        k_prefix<<<1, 32, 0, st>>>(pdf_x, W, cdf_x);
+        k_transpose<<<dim3((W + 31) / 32, (H + 31) / 32), dim3(32, 8), 0, st>>>(cdf_y, W, H, cdf_yT);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    }
+    cudaFree(cdf_y); cudaFree(small);
+    if (e != cudaSuccess) { cudaFree(pdf); cudaFree(cdf_yT); cudaFree(cdf_x); return e; }
+    *pdf_out = pdf; *cdf_x_out = cdf_x; *cdf_yT_out = cdf_yT;
+    return cudaSuccess;
+}
 
 // d_rgb: W*H*3 floats on the device (file row order).  Exactly one of d_cache4 (W*H float4, the renderer's layout) and
 // d_cache3 (W*H*3 floats, the reference's layout) receives the table.  Temporaries are allocated and freed here.

@@ -12,6 +12,8 @@ cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool coun
     if (count) return launch_persistent<CfgFastCount>(p, variant, grid, stream);
     return launch_persistent<CfgFast>(p, variant, grid, stream);
 }
+// PT_ENV_CDF_SEARCH: variant 2 on the persistent pipeline only
+cudaError_t launch_persistent_fast_cdf(const RenderParams& p, int grid, cudaStream_t stream) { return launch_persistent_variant<CfgFastCdf, 2>(p, grid, stream); }
 cudaError_t launch_wavefront_fast(const RenderParams& p, int variant, bool count, int num_sms, cudaStream_t stream, WaveStats* ws) {
     if (count) return launch_wavefront<CfgFastCount>(p, variant, num_sms, stream, ws);
     return launch_wavefront<CfgFast>(p, variant, num_sms, stream, ws);

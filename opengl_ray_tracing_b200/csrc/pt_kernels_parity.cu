@@ -16,6 +16,7 @@ cudaError_t launch_persistent_parity(const RenderParams& p, int variant, int whi
     if (which == 2) return launch_persistent<CfgParityWide>(p, variant, grid, stream);
     return launch_persistent<CfgParityFast>(p, variant, grid, stream);
 }
+cudaError_t launch_persistent_parity_cdf(const RenderParams& p, int grid, cudaStream_t stream) { return launch_persistent_variant<CfgParityFastCdf, 2>(p, grid, stream); }
 // the wavefront pipeline under the parity arithmetic: which = 2 (reference topology, wide nodes) or 3 (fast topology)
 cudaError_t launch_wavefront_parity(const RenderParams& p, int variant, int which, int num_sms, cudaStream_t stream, WaveStats* ws) {
     if (which == 2) return launch_wavefront<CfgParityWide>(p, variant, num_sms, stream, ws);

@@ -65,11 +65,14 @@ struct MathFast {
     static __device__ __forceinline__ float pow_dir(float a, float b) { return __powf(a, b); }
 #endif
 };
-struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = false; };
-struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = true; };
-struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true; };
-struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true; };
-struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  static const bool LIGHT_TAB = true; };
+struct CfgParityRef  { typedef MathExact M; static const bool RAW = true;  static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = false; static const bool ENV_CDF = false; };
+struct CfgParityWide { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = false; static const bool COUNT = false; static const bool LIGHT_TAB = true;  static const bool ENV_CDF = false; };
+struct CfgParityFast { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true;  static const bool ENV_CDF = false; };
+struct CfgFast       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = false; static const bool LIGHT_TAB = true;  static const bool ENV_CDF = false; };
+struct CfgFastCount  { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true;  static const bool COUNT = true;  static const bool LIGHT_TAB = true;  static const bool ENV_CDF = false; };
+// PT_ENV_CDF_SEARCH: light samples by binary search of the marginal / conditional CDFs (no hdrCache table, no light table)
+struct CfgParityFastCdf { typedef MathExact M; static const bool RAW = false; static const bool FAST_TREE = true; static const bool COUNT = false; static const bool LIGHT_TAB = false; static const bool ENV_CDF = true; };
+struct CfgFastCdf       { typedef MathFast  M; static const bool RAW = false; static const bool FAST_TREE = true; static const bool COUNT = false; static const bool LIGHT_TAB = false; static const bool ENV_CDF = true; };
 
 // counting configuration: histogram of traversal steps (inner nodes + triangles) per ray, log2 buckets
 __device__ __forceinline__ uint32_t ray_steps(const Counter<false>&) { return 0; }
@@ -185,20 +188,25 @@ template <class M> __device__ __forceinline__ V3 sampleHdr(const DevScene& sc, V
     return mk3(fminf(c.x, 10.0f), fminf(c.y, 10.0f), fminf(c.z, 10.0f));
 }
 // hdrColor (unclamped, P:647-651) and hdrPdf (P:655-666) look up the same uv: one atan2/asin for both
-template <class M> __device__ __forceinline__ void hdr_color_pdf(const DevScene& sc, V3 L, V3& color, float& pdf_light) {
+// the table's B channel (pdf of the texel): from the hdrCache texture, or (PT_ENV_CDF_SEARCH) from the pdf map itself
+template <bool CDF> __device__ __forceinline__ float env_texel_pdf(const DevScene& sc, float u, float w) {
+    if (CDF) return ldg1(sc.env_pdf + (size_t)nearest_texel(w, sc.hdrH) * sc.hdrW + nearest_texel(u, sc.hdrW));
+    return tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, u, w).z;
+}
+template <class M, bool CDF = false> __device__ __forceinline__ void hdr_color_pdf(const DevScene& sc, V3 L, V3& color, float& pdf_light) {
     float u, w;
     spherical_uv(L, u, w);
     float4 c = tex_nearest(sc.hdr4, sc.hdrW, sc.hdrH, u, w);
     color = mk3(c.x, c.y, c.z);
-    float pdf = tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, u, w).z;
+    float pdf = env_texel_pdf<CDF>(sc, u, w);
     float theta = PT_PI * (0.5f - w);
     float sin_theta = fmaxf(M::sin(theta), 1e-10f);
     float p_convert = (float)(sc.hdrW * sc.hdrW / 2) / (2.0f * PT_PI * PT_PI * sin_theta);
     pdf_light = pdf * p_convert;
 }
 // hdrPdf at an already computed uv, P:655-666
-template <class M> __device__ __forceinline__ float hdr_pdf(const DevScene& sc, float u, float w) {
-    float pdf = tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, u, w).z;
+template <class M, bool CDF = false> __device__ __forceinline__ float hdr_pdf(const DevScene& sc, float u, float w) {
+    float pdf = env_texel_pdf<CDF>(sc, u, w);
     float theta = PT_PI * (0.5f - w);
     float sin_theta = fmaxf(M::sin(theta), 1e-10f);
     float p_convert = (float)(sc.hdrW * sc.hdrW / 2) / (2.0f * PT_PI * PT_PI * sin_theta);
@@ -211,7 +219,29 @@ __device__ __forceinline__ V3 hdr_entry_direction(float4 c) {                   
     float ct = pt_cosf(theta);
     return mk3(s_mul(ct, pt_cosf(phi)), pt_sinf(theta), s_mul(ct, pt_sinf(phi)));
 }
-template <class M> __device__ __forceinline__ V3 SampleHdr(const DevScene& sc, float xi_1, float xi_2) {   // P:573-585
+// std::lower_bound as libstdc++ writes it (first position whose element is not < val)
+__device__ __forceinline__ int lower_bound_ldg(const float* __restrict__ a, int n, float val) {
+    int first = 0, len = n;
+    while (len > 0) {
+        const int half = len >> 1, middle = first + half;
+        if (ldg1(a + middle) < val) { first = middle + 1; len = len - half - 1; }
+        else len = half;
+    }
+    return first;
+}
+// SampleHdr, P:573-585.  CDF = false: the reference's NEAREST lookup in the precomputed table.  CDF = true
+// (PT_ENV_CDF_SEARCH): the two searches calculateHdrCache ran per table entry (M:621-636) run per sample on the continuous
+// random numbers.  The table entry a lookup (xi_1, xi_2) reads is [row floor(xi_2 H)][column floor(xi_1 W)], which the
+// reference computed from "xi_1" = row / H and "xi_2" = column / W (its transposed roles, M:616-634): so xi_2 searches the
+// marginal CDF for the column x and xi_1 the column's conditional CDF for the row y — at the table's grid points the
+// search returns the table's entries (tests/test_env_cdf.py).
+template <class M, bool CDF = false> __device__ __forceinline__ V3 SampleHdr(const DevScene& sc, float xi_1, float xi_2) {   // P:573-585
+    if (CDF) {
+        int x = lower_bound_ldg(sc.env_cdf_x, sc.hdrW, xi_2);
+        if (x >= sc.hdrW) x = sc.hdrW - 1;
+        const int y = lower_bound_ldg(sc.env_cdf_y + (size_t)x * sc.hdrH, sc.hdrH, xi_1);
+        return hdr_entry_direction(make_float4(s_div((float)x, (float)sc.hdrW), s_div((float)y, (float)sc.hdrH), 0.0f, 0.0f));
+    }
     return hdr_entry_direction(tex_nearest(sc.cache4, sc.hdrW, sc.hdrH, xi_1, xi_2));
 }
 
@@ -588,7 +618,7 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
             if (phase == PT_PH_PRIMARY) return mk3(fminf(c.x, 10.0f), fminf(c.y, 10.0f), fminf(c.z, 10.0f));   // P:857-859
             if (VARIANT == 2) {
                 const V3 color = mk3(c.x, c.y, c.z);                                                  // hdrColor, P:647-651
-                const float pdf_light = hdr_pdf<M>(sc, u, w);                                         // hdrPdf, P:655-666
+                const float pdf_light = hdr_pdf<M, Cfg::ENV_CDF>(sc, u, w);                           // hdrPdf, P:655-666
                 if (!Cfg::LIGHT_TAB && phase == PT_PH_SHADOW) {                                       // P:781-792
                     const float mis_weight = misMixWeight(pdf_light, pdf_b);
                     Lo = Lo + (history * mis_weight) * color * fl * ndl / pdf_light;
@@ -629,10 +659,10 @@ __device__ __forceinline__ V3 shade_sample(const RenderParams& p, int px, int py
                 V3 Ld;
                 if (Cfg::LIGHT_TAB) {
                     light_idx = (uint32_t)nearest_texel(e2, sc.hdrH) * (uint32_t)sc.hdrW + (uint32_t)nearest_texel(e1, sc.hdrW);
-                    const float4 r0 = ldg4(sc.light_tab + 2 * (size_t)light_idx);
+                    const float4 r0 = ldg4(sc.light_tab + 2 * (size_t)PT_IDX(sc, light_idx, (size_t)sc.hdrW * sc.hdrH));
                     Ld = mk3(r0.x, r0.y, r0.z);
                 } else {
-                    Ld = SampleHdr<M>(sc, e1, e2);
+                    Ld = SampleHdr<M, Cfg::ENV_CDF>(sc, e1, e2);
                 }
                 cnt.texel(1u);
                 ndl = dot(N, Ld);
@@ -855,7 +885,7 @@ __global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) rende
             }
             // ordered accumulation
             if (valid) {
-                float4* const slot = p.accum + (size_t)py * p.width + px;
+                float4* const slot = p.accum + PT_IDX(p.sc, (size_t)py * p.width + px, (size_t)p.width * p.height);
                 uint4 raw = ld_relaxed_v4(slot);
                 if (fa != 0u) {
                     const uint32_t want = PT_TAG | (fa & 0x3fffffu);
@@ -894,17 +924,17 @@ __global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) rende
     flush_counts(cnt, p.work_counters);
 }
 
-template <class Cfg>
-cudaError_t launch_persistent(const RenderParams& p, int variant, int num_sms, cudaStream_t stream) {
+template <class Cfg, int VARIANT>
+cudaError_t launch_persistent_variant(const RenderParams& p, int num_sms, cudaStream_t stream) {
     const TileMap tm = make_tile_map(p.x0, p.y0, p.x1, p.y1, p.band_world, p.band_rank, p.band_diag);
     const size_t ntiles = tm.count();
     if (ntiles == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(p.sched, 0, 64 * sizeof(uint32_t), stream);   // the work head (its own 256 bytes)
     if (e != cudaSuccess) return e;
-    if (variant == 2 && p.sobol_tab)
+    if (VARIANT == 2 && p.sobol_tab)
         sobol_table_kernel<<<(p.n_frames * 8 + 255) / 256, 256, 0, stream>>>(const_cast<float*>(p.sobol_tab), p.first_frame, p.n_frames, p.frame_stride);
     // one resident set of CTAs: SMs x (CTAs that fit per SM), never more warps than there are tiles
-    void (*kern)(const RenderParams) = variant == 0 ? render_persistent<Cfg, 0> : variant == 1 ? render_persistent<Cfg, 1> : render_persistent<Cfg, 2>;
+    void (*kern)(const RenderParams) = render_persistent<Cfg, VARIANT>;
     int per_sm = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PT_PERSIST_THREADS, 0);
     if (e != cudaSuccess) return e;
@@ -913,6 +943,12 @@ cudaError_t launch_persistent(const RenderParams& p, int variant, int num_sms, c
     if (grid > need) grid = need;
     kern<<<grid, PT_PERSIST_THREADS, 0, stream>>>(p);
     return cudaGetLastError();
+}
+template <class Cfg>
+cudaError_t launch_persistent(const RenderParams& p, int variant, int num_sms, cudaStream_t stream) {
+    if (variant == 0) return launch_persistent_variant<Cfg, 0>(p, num_sms, stream);
+    if (variant == 1) return launch_persistent_variant<Cfg, 1>(p, num_sms, stream);
+    return launch_persistent_variant<Cfg, 2>(p, num_sms, stream);
 }
 
 template <class Cfg>

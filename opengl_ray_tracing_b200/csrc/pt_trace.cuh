@@ -294,36 +294,26 @@ template <> struct Counter<false> {
 #ifndef PT_STACK_TOS
 #define PT_STACK_TOS 0
 #endif
-#define PT_STACK_STRIDE 256           // threads per CTA of every kernel that traverses (static_assert in pt_shade.cuh)
-template <int STACK>
+#define PT_STACK_STRIDE 256           // threads per CTA of every kernel that traverses
+template <int STACK, int SMEM>
 struct TravStack {
-    uint32_t local[STACK > PT_SMEM_STACK ? STACK - PT_SMEM_STACK : 1];
-#if PT_SMEM_STACK > 0
+    uint32_t local[STACK > SMEM ? STACK - SMEM : 1];
     uint32_t* sm;
-#endif
 #if PT_STACK_TOS
     uint32_t tos;
 #endif
     int sp;
     __device__ __forceinline__ void init(uint32_t* smem_base) {
         sp = 0;
-#if PT_SMEM_STACK > 0
-        sm = smem_base + threadIdx.x;
-#else
-        (void)smem_base;
-#endif
+        sm = SMEM > 0 ? smem_base + threadIdx.x : nullptr;
     }
     __device__ __forceinline__ void put(int k, uint32_t v) {
-#if PT_SMEM_STACK > 0
-        if (k < PT_SMEM_STACK) { sm[k * PT_STACK_STRIDE] = v; return; }
-#endif
-        if (STACK > PT_SMEM_STACK) local[k - PT_SMEM_STACK] = v;
+        if (SMEM > 0 && k < SMEM) { sm[k * PT_STACK_STRIDE] = v; return; }
+        if (STACK > SMEM) local[k - SMEM] = v;
     }
     __device__ __forceinline__ uint32_t get(int k) const {
-#if PT_SMEM_STACK > 0
-        if (k < PT_SMEM_STACK) return sm[k * PT_STACK_STRIDE];
-#endif
-        return STACK > PT_SMEM_STACK ? local[k - PT_SMEM_STACK] : PT_REF_NONE;
+        if (SMEM > 0 && k < SMEM) return sm[k * PT_STACK_STRIDE];
+        return STACK > SMEM ? local[k - SMEM] : PT_REF_NONE;
     }
     __device__ __forceinline__ bool full() const { return sp >= STACK; }
     __device__ __forceinline__ bool empty() const { return sp == 0; }
@@ -372,13 +362,14 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
 #else
     uint32_t* const smem_base = nullptr;
 #endif
-    TravStack<STACK> stk;
+    TravStack<STACK, PT_SMEM_STACK> stk;
     stk.init(smem_base);
     uint32_t ref = sc.root_fast;
     while (true) {
         while (ref_count(ref) == 0) {                 // inner node: both child boxes and refs in one 64-byte record
-            const float4* w = sc.wnodes_fast + 4 * (size_t)ref;
-            const float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
+            const float4* w = sc.wnodes_fast + 4 * (size_t)PT_IDX(sc, ref, sc.nFastInner);
+            float4 q0, q1, q2, q3;
+            ldg8(w, q0, q1); ldg8(w + 2, q2, q3);
             cnt.inner();
             float e1, e2;
             const bool g1 = slab_cull_fused(cr, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), cull, e1);
@@ -398,16 +389,17 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
         if (ref != PT_REF_NONE) {                     // leaf: hitArray over its (re-ordered) triangles
             const uint32_t first = ref_index(ref), end = first + ref_count(ref);
             for (uint32_t i = first; i < end; i++) {
-                const float4* g = sc.trigeo_fast + 3 * (size_t)i;
-                const float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2);
+                const float4* g = sc.trigeo_fast + 4 * (size_t)PT_IDX(sc, i, sc.nTriangles);
+                float4 a, b, c, m4;
+                ldg8(g, a, b); ldg8(g + 2, c, m4);
                 cnt.tri();
                 float tt; bool ins;
                 if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), mk3(a.w, b.w, c.w), res.t, tt, ins,
                                  !anyhit && res.tri >= 0)) {
                     cnt.cand();
-                    const int2 meta = __ldg(sc.trimeta + i);
+                    const int2 meta = make_int2(__float_as_int(m4.x), __float_as_int(m4.y));
                     if (meta.y != 1) {                // the reference never box-tests its root (P:342-343)
-                        const float* nd = sc.nodes_raw + 12 * (size_t)meta.y;
+                        const float* nd = sc.nodes_raw + 12 * (size_t)PT_IDX(sc, meta.y, sc.nNodes);
                         float e;
                         r.inv = mk3(s_rcp(dir.x), s_rcp(dir.y), s_rcp(dir.z));
                         if (!(hit_aabb(r, raw3(nd + 6), raw3(nd + 9), e) > 0.0f)) continue;
@@ -455,8 +447,8 @@ __device__ __forceinline__ void finalize_hit(const DevScene& sc, V3 origin, V3 d
         p1 = raw3(t); p2 = raw3(t + 3); p3 = raw3(t + 6); n1 = raw3(t + 9); n2 = raw3(t + 12); n3 = raw3(t + 15);
         mat_id = tr.tri;                              // material read from the triangle record itself
     } else {
-        const float4* g = sc.trigeo + 3 * (size_t)tr.tri;
-        const float4* s = sc.trishade + 3 * (size_t)tr.tri;
+        const float4* g = sc.trigeo + 3 * (size_t)PT_IDX(sc, tr.tri, sc.nTriangles);
+        const float4* s = sc.trishade + 3 * (size_t)PT_IDX(sc, tr.tri, sc.nTriangles);
         float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2), u = ldg4(s), v = ldg4(s + 1), w = ldg4(s + 2);
         p1 = mk3(a.x, a.y, a.z); p2 = mk3(b.x, b.y, b.z); p3 = mk3(c.x, c.y, c.z);
         n1 = mk3(u.x, u.y, u.z); n2 = mk3(v.x, v.y, v.z); n3 = mk3(w.x, w.y, w.z);
@@ -483,7 +475,7 @@ __device__ __forceinline__ void load_material(const DevScene& sc, int mat_id, Ma
         m.specularTint = ldg1(t + 9); m.roughness = ldg1(t + 10); m.anisotropic = ldg1(t + 11);
         m.sheen = ldg1(t + 12); m.sheenTint = ldg1(t + 13); m.clearcoat = ldg1(t + 14); m.clearcoatGloss = ldg1(t + 15);
     } else {
-        const float4* p = sc.materials + 8 * (size_t)mat_id;      // 128-byte records: 4 float4 as uploaded, 4 derived (pt_shade.cuh)
+        const float4* p = sc.materials + 8 * (size_t)PT_IDX(sc, mat_id, sc.nMaterials);      // 128-byte records: 4 float4 as uploaded, 4 derived (pt_shade.cuh)
         float4 a = ldg4(p), b = ldg4(p + 1), c = ldg4(p + 2), d = ldg4(p + 3);
         m.emissive = mk3(a.x, a.y, a.z); m.subsurface = a.w;
         m.baseColor = mk3(b.x, b.y, b.z); m.metallic = b.w;

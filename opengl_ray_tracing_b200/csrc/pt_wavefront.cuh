@@ -46,6 +46,9 @@ namespace pt {
 #ifndef PT_WF_TRACE_CTAS
 #define PT_WF_TRACE_CTAS 4        // resident CTAs (256 threads) per SM the traversal kernel is compiled for (4: 64 registers)
 #endif
+#ifndef PT_WF_SMEM_STACK
+#define PT_WF_SMEM_STACK 0        // wf_trace: traversal-stack entries per thread kept in shared memory (TravStack, pt_trace.cuh)
+#endif
 #ifndef PT_WF_NODE_BIAS
 #define PT_WF_NODE_BIAS 0         // wf_trace's vote: a node step runs when (lanes at nodes) + bias >= (lanes at triangles)
 #endif
@@ -158,7 +161,7 @@ __device__ __forceinline__ WfNext wf_shade_hit(const RenderParams& p, uint32_t s
             const float4 r0 = ldg4(sc.light_tab + 2 * (size_t)light_idx);
             Ld = mk3(r0.x, r0.y, r0.z);
         } else {
-            Ld = SampleHdr<M>(sc, e1, e2);
+            Ld = SampleHdr<M, Cfg::ENV_CDF>(sc, e1, e2);
         }
         cnt.texel(1u);
         const float ndl = dot(N, Ld);
@@ -189,7 +192,7 @@ __device__ __forceinline__ WfNext wf_shade_hit(const RenderParams& p, uint32_t s
                 const float4 e = ldg4(sc.light_tab + 2 * (size_t)light_idx + 1);
                 color = mk3(e.x, e.y, e.z); pdf_light = e.w;
             } else {
-                hdr_color_pdf<M>(sc, Ld, color, pdf_light);
+                hdr_color_pdf<M, Cfg::ENV_CDF>(sc, Ld, color, pdf_light);
             }
             cnt.texel(2u);
             const float mis_weight = misMixWeight(pdf_light, pdf_b);
@@ -249,7 +252,7 @@ __global__ void __launch_bounds__(256, PT_WF_HEAD_CTAS) wf_head(const __grid_con
         const bool valid = px < p.x1 && py < p.y1;
         const uint32_t frame = p.first_frame + (f0 + fl) * p.frame_stride;
         const size_t idx = (size_t)py * p.width + px;
-        const uint32_t islot = fl * wf.npix + (uint32_t)idx;
+        const uint32_t islot = (uint32_t)PT_IDX(p.sc, (size_t)fl * wf.npix + idx, valid ? wf.icap : ~(size_t)0);
         uint32_t seed = ((uint32_t)px * 1973u + (uint32_t)py * 9277u + frame * 26699u) | 1u;             // P:73-76
         V3 o = mk3(0, 0, 0), d = mk3(0, 0, 1);
         TraceResult tr; tr.tri = -1; tr.t = PT_INF; tr.inside = false;
@@ -359,7 +362,7 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
     float cull = PT_INF;
     bool tie = false;
     uint32_t steps = 0;
-    TravStack<PT_STACK> stk;
+    TravStack<PT_STACK, PT_WF_SMEM_STACK> stk;
     stk.init(smem_stack);
     uint32_t ref = PT_REF_NONE;                        // NODE: the inner node to fetch
     uint32_t ti = 0, tend = 0;                         // TRI: the next triangle of the leaf, and the leaf's end
@@ -390,8 +393,8 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
                     const uint32_t take = min(n_idle, chunk_end - chunk_next);
                     const uint32_t rank = (uint32_t)__popc(idle & lt);
                     if (mode == PT_WF_MODE_NONE && rank < take) {
-                        qi = chunk_next + rank;
-                        const uint32_t entry = wf.q_ray[qi], slot = entry & ~PT_WF_SHADOW_BIT;
+                        qi = (uint32_t)PT_IDX(sc, chunk_next + rank, 2 * wf.pcap);
+                        const uint32_t entry = wf.q_ray[qi], slot = (uint32_t)PT_IDX(sc, entry & ~PT_WF_SHADOW_BIT, wf.pcap);
                         anyhit = (entry & PT_WF_SHADOW_BIT) != 0;
                         const float4 o4 = wf.ray_o[slot];
                         const float4 d4 = anyhit ? wf.sh_d[slot] : wf.ray_d[slot];
@@ -418,8 +421,9 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
         if (__popc(m_node) + PT_WF_NODE_BIAS >= __popc(m_tri)) {
             // ---- node step: both child boxes and refs in one 64-byte record ----
             if (mode == PT_WF_MODE_NODE) {
-                const float4* w = sc.wnodes_fast + 4 * (size_t)ref;
-                const float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
+                const float4* w = sc.wnodes_fast + 4 * (size_t)PT_IDX(sc, ref, sc.nFastInner);
+                float4 q0, q1, q2, q3;
+                ldg8(w, q0, q1); ldg8(w + 2, q2, q3);
                 cnt.inner();
                 if (Cfg::COUNT) steps++;
                 float e1, e2;
@@ -438,9 +442,11 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
         } else {
             // ---- triangle step: hitArray, one triangle per turn ----
             if (mode == PT_WF_MODE_TRI) {
-                const uint32_t i = ti++;
-                const float4* g = sc.trigeo_fast + 3 * (size_t)i;
-                const float4 a = ldg4(g), bq = ldg4(g + 1), c = ldg4(g + 2);
+                const uint32_t i = (uint32_t)PT_IDX(sc, ti, sc.nTriangles);
+                ti++;
+                const float4* g = sc.trigeo_fast + 4 * (size_t)i;
+                float4 a, bq, c, m4;
+                ldg8(g, a, bq); ldg8(g + 2, c, m4);
                 cnt.tri();
                 if (Cfg::COUNT) steps++;
                 float tt; bool ins;
@@ -448,10 +454,10 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
                 if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(bq.x, bq.y, bq.z), mk3(c.x, c.y, c.z), mk3(a.w, bq.w, c.w), res.t, tt, ins,
                                  !anyhit && res.tri >= 0)) {
                     cnt.cand();
-                    const int2 meta = __ldg(sc.trimeta + i);
+                    const int2 meta = make_int2(__float_as_int(m4.x), __float_as_int(m4.y));
                     bool accept = true;
                     if (meta.y != 1) {                // the reference never box-tests its root (P:342-343)
-                        const float* nd = sc.nodes_raw + 12 * (size_t)meta.y;
+                        const float* nd = sc.nodes_raw + 12 * (size_t)PT_IDX(sc, meta.y, sc.nNodes);
                         float e;
                         r.inv = mk3(s_rcp(r.d.x), s_rcp(r.d.y), s_rcp(r.d.z));
                         accept = hit_aabb(r, raw3(nd + 6), raw3(nd + 9), e) > 0.0f;
@@ -485,8 +491,8 @@ __device__ __forceinline__ void wf_trace_refill(const RenderParams& p, int b, ui
 template <class Cfg>
 __global__ void __launch_bounds__(256, PT_WF_TRACE_CTAS) wf_trace(const __grid_constant__ RenderParams p, int b) {
     const WaveBuffers& wf = p.wf;
-#if PT_SMEM_STACK > 0
-    __shared__ uint32_t s_stack[PT_SMEM_STACK * PT_STACK_STRIDE];
+#if PT_WF_SMEM_STACK > 0
+    __shared__ uint32_t s_stack[PT_WF_SMEM_STACK * PT_STACK_STRIDE];
     uint32_t* const smem_stack = s_stack;
 #else
     uint32_t* const smem_stack = nullptr;
@@ -514,7 +520,7 @@ static __global__ void __launch_bounds__(256) wf_classify(const __grid_constant_
         if (i < count) {
             const uint32_t e = wf.q_ray[i];
             const int2 r = wf.res[i];
-            slot = e & ~PT_WF_SHADOW_BIT;
+            slot = (uint32_t)PT_IDX(p.sc, e & ~PT_WF_SHADOW_BIT, wf.pcap);
             if (e & PT_WF_SHADOW_BIT) {
                 if (r.x != -1) wf.cs[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
             } else if (r.x != -1) {
@@ -550,14 +556,14 @@ __global__ void __launch_bounds__(256, PT_WF_HEAD_CTAS) wf_shade(const __grid_co
                 WfNext nx; nx.shadow = nx.extend = nx.to_miss = false;
                 uint32_t slot = 0;
                 if (i < count) {
-                    slot = wf.q_hit[i];
+                    slot = (uint32_t)PT_IDX(sc, wf.q_hit[i], wf.pcap);
                     const float4 ro = wf.ray_o[slot], rd = wf.ray_d[slot], hs = wf.hist[slot], fr = wf.fr[slot], lo4 = wf.lo[slot];
                     const int2 hr = wf.hit[slot];
                     TraceResult tr;
                     tr.tri = hr.x & 0x7fffffff; tr.inside = hr.x < 0; tr.t = __int_as_float(hr.y);
                     V3 Lo = xyz(lo4);
                     if (__float_as_uint(fr.w) & PT_WF_FLAG_SHADOW) Lo = Lo + xyz(wf.cs[slot]);            // the light term of bounce b-1, in order
-                    const uint32_t islot = wf.pix[slot];
+                    const uint32_t islot = (uint32_t)PT_IDX(sc, wf.pix[slot], wf.icap);
                     const uint32_t fl = islot / wf.npix, idx = islot - fl * wf.npix;
                     const int px = (int)(idx % (uint32_t)p.width), py = (int)(idx / (uint32_t)p.width);
                     const uint32_t frame = p.first_frame + (f0 + fl) * p.frame_stride;
@@ -578,7 +584,7 @@ __global__ void __launch_bounds__(256, PT_WF_HEAD_CTAS) wf_shade(const __grid_co
             for (uint32_t k = 0; k < 64u; k += 32) {
                 const uint32_t i = base + k + lane;
                 if (i >= count) continue;
-                const uint32_t slot = wf.q_miss[(b - 1) & 1][i];
+                const uint32_t slot = (uint32_t)PT_IDX(sc, wf.q_miss[(b - 1) & 1][i], wf.pcap);
                 const float4 fr = wf.fr[slot], lo4 = wf.lo[slot];
                 const uint32_t flags = __float_as_uint(fr.w);
                 V3 Lo = xyz(lo4);
@@ -593,7 +599,7 @@ __global__ void __launch_bounds__(256, PT_WF_HEAD_CTAS) wf_shade(const __grid_co
                     cnt.texel(VARIANT == 2 ? 2u : 1u);
                     if (VARIANT == 2) {                                                                   // P:819-830
                         const V3 color = mk3(c.x, c.y, c.z);
-                        const float pdf_light = hdr_pdf<M>(sc, u, w);
+                        const float pdf_light = hdr_pdf<M, Cfg::ENV_CDF>(sc, u, w);
                         const float mis_weight = misMixWeight(pdf, pdf_light);
                         Lo = Lo + (history * mis_weight) * color * f_r * cosw / pdf;
                     } else {                                                                              // O:349-353, D:465-469
@@ -601,7 +607,7 @@ __global__ void __launch_bounds__(256, PT_WF_HEAD_CTAS) wf_shade(const __grid_co
                         Lo = Lo + history * sky * f_r * cosw / pdf;
                     }
                 }
-                wf_finish<Cfg>(p, wf.pix[slot], Lo, __float_as_int(lo4.w));
+                wf_finish<Cfg>(p, (uint32_t)PT_IDX(sc, wf.pix[slot], wf.icap), Lo, __float_as_int(lo4.w));
             }
         }
     }

@@ -25,6 +25,7 @@ ACC_MEAN, ACC_SUM = 0, 1
 COMBINE_SUM, COMBINE_DISJOINT, COMBINE_DISPLAY = 0, 1, 4
 COMM_ID_BYTES = 128
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
+ENV_TABLE, ENV_CDF_SEARCH = 0, 1
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
            "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_measure_l2_read_gbs", "pt_kernel_sass_hash", "pt_comm_get_unique_id", "pt_comm_init", "pt_comm_info", "pt_comm_destroy", "pt_combine", "pt_last_error",
@@ -33,7 +34,7 @@ EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_se
 
 class PtConfig(C.Structure):
     _fields_ = [("variant", C.c_int), ("width", C.c_int), ("height", C.c_int), ("max_bounce", C.c_int),
-                ("device", C.c_int), ("mode", C.c_int), ("pipeline", C.c_int)]
+                ("device", C.c_int), ("mode", C.c_int), ("pipeline", C.c_int), ("env_sampler", C.c_int)]
 
 
 class PtStats(C.Structure):
@@ -114,10 +115,11 @@ def _fp(a):
 class PathTracer:
     """pass1 of the reference (shader variant ``variant``) on CUDA device ``device``."""
 
-    def __init__(self, width, height, variant=DISNEY_IS_MIS, max_bounce=0, device=0, mode=MODE_FAST, pipeline=PERSISTENT):
+    def __init__(self, width, height, variant=DISNEY_IS_MIS, max_bounce=0, device=0, mode=MODE_FAST, pipeline=PERSISTENT,
+                 env_sampler=ENV_TABLE):
         self.width, self.height, self.variant, self.mode = width, height, variant, mode
         self.pipeline = pipeline
-        cfg = PtConfig(variant, width, height, max_bounce, device, mode, pipeline)
+        cfg = PtConfig(variant, width, height, max_bounce, device, mode, pipeline, env_sampler)
         h = C.c_void_p()
         _check(lib().pt_create(C.byref(cfg), C.byref(h)), "pt_create")
         self._h = h

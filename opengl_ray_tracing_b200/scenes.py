@@ -78,6 +78,19 @@ def _populate(sc: S.Scene, kind: str, freq: int):
 
 
 KINDS = {"lambert": (0, 2), "disney": (1, 5), "is": (2, 2), "full": (0, 2)}
+LEAF_N = 8                                                       # buildBVH*(…, 8), M:787-788
+
+
+def _builder_fingerprint() -> str:
+    """What a cached scene depends on besides (kind, frequency, builder): the scene literals of _populate above and the
+    sources of the host library that generates the meshes and builds the trees.  A change to any of them changes the key."""
+    import inspect
+    h = hashlib.sha1(inspect.getsource(_populate).encode())
+    here = os.path.dirname(os.path.abspath(__file__))
+    for name in ("pts_bvh.cpp", "pts_meshgen.cpp", "pts_scene.cpp", "pts_scene.h", "pts_math.h"):
+        with open(os.path.join(here, "csrc", "scene", name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:12]
 
 
 def build(kind: str, size: str = "10k", hdr_res=(1024, 512), hdr_path: str | None = None, threads: int | None = None,
@@ -91,7 +104,7 @@ def build(kind: str, size: str = "10k", hdr_res=(1024, 512), hdr_path: str | Non
     os.makedirs(CACHE_DIR, exist_ok=True)
     # builder "sah" = buildBVHwithSAH (what the reference's main() calls, M:788); "median" = buildBVH, the alternative the
     # reference keeps commented out one line above (M:787) — seconds instead of hours at 10 M triangles
-    key = hashlib.sha1(("%s-%d-v3%s" % (kind, freq, "" if builder == "sah" else "-" + builder)).encode()).hexdigest()[:16]
+    key = hashlib.sha1(("%s-%d-%s-leaf%d-%s" % (kind, freq, builder, LEAF_N, _builder_fingerprint())).encode()).hexdigest()[:16]
     path = os.path.join(CACHE_DIR, "%s_%d_%s.ptsc" % (kind, freq, key))
     sc = S.Scene()
     if use_cache and os.path.exists(path):
@@ -99,11 +112,13 @@ def build(kind: str, size: str = "10k", hdr_res=(1024, 512), hdr_path: str | Non
     else:
         _populate(sc, kind, freq)
         if builder == "sah":
-            sc.buildBVHwithSAH(8, threads)                       # M:788
+            sc.buildBVHwithSAH(LEAF_N, threads)                  # M:788
         else:
-            sc.buildBVH(8, threads)                              # M:787
+            sc.buildBVH(LEAF_N, threads)                         # M:787
         if use_cache:
-            sc.save(path)
+            tmp = "%s.%d.tmp" % (path, os.getpid())              # atomic: another rank may be waiting to load this file
+            sc.save(tmp)
+            os.replace(tmp, path)
     tris, nodes = sc.triangles_encoded(), sc.nodes_encoded()
     sc.close()
     if hdr_path:

@@ -48,8 +48,11 @@ def lib():
 
 
 def render(variant, max_bounce, tris, nodes, hdr, hdrCache, width, height, eye, cam, first_frame, n_frames,
-           accum=None, math=1, counters=False, region=None):
-    """Returns (accum [H,W,4] float32, primary_ids [H,W] int32 of the last frame, counters dict or None)."""
+           accum=None, math=1, counters=False, region=None, env_sampler=0):
+    """Returns (accum [H,W,4] float32, primary_ids [H,W] int32 of the last frame, counters dict or None).
+    env_sampler = 1: variant 2 picks its light samples by per-sample CDF binary search (the product's ENV_CDF_SEARCH)
+    instead of the reference's hdrCache table lookup."""
+    lib().oracle_set_env_sampler(int(env_sampler))
     tris = np.ascontiguousarray(tris, np.float32); nodes = np.ascontiguousarray(nodes, np.float32)
     hdr = np.ascontiguousarray(hdr, np.float32)
     hc = np.ascontiguousarray(hdrCache, np.float32) if hdrCache is not None else None
@@ -62,11 +65,28 @@ def render(variant, max_bounce, tris, nodes, hdr, hdrCache, width, height, eye, 
     rc = lib().oracle_render(variant, max_bounce, math, _fp(tris), len(tris), _fp(nodes), len(nodes), _fp(hdr), _fp(hc),
                              hdr.shape[1], hdr.shape[0], width, height, _fp(eye), _fp(cam), C.c_uint(first_frame),
                              C.c_uint(n_frames), _fp(accum), ids.ctypes.data_as(C.POINTER(C.c_int)), cnt, x0, y0, x1, y1)
+    lib().oracle_set_env_sampler(0)
     if rc == -2:
         raise OverflowError("oracle: a ray needed more than 16384 traversal stack entries")
     if rc != 0:
         raise RuntimeError("oracle_render rejected its arguments")
     return accum, ids, (dict(zip(COUNTER_NAMES, [int(v) for v in cnt])) if counters else None)
+
+
+def env_cdf_sample(hdr, xi):
+    """Texels (x, y) the CDF-search sampler picks for the random pairs xi [n, 2]."""
+    hdr = np.ascontiguousarray(hdr, np.float32); xi = np.ascontiguousarray(xi, np.float32)
+    out = np.empty((len(xi), 2), np.int32)
+    lib().oracle_env_cdf_sample(_fp(hdr), hdr.shape[1], hdr.shape[0], len(xi), _fp(xi), out.ctypes.data_as(C.POINTER(C.c_int)))
+    return out
+
+
+def env_pdf(hdr):
+    """calculateHdrCache's per-texel pdf (its B channel), [H, W]."""
+    hdr = np.ascontiguousarray(hdr, np.float32)
+    out = np.empty(hdr.shape[:2], np.float32)
+    lib().oracle_env_pdf(_fp(hdr), hdr.shape[1], hdr.shape[0], _fp(out))
+    return out
 
 
 def wang_hash_seq(px, py, frame, n):

@@ -41,7 +41,7 @@ def test_libptscene_exports_every_declared_symbol():
 def test_build_info_and_struct_layouts():
     info = R.build_info()
     assert "sm_100a" in info
-    assert C.sizeof(R.PtConfig) == 28 and C.sizeof(R.PtStats) == 112 and C.sizeof(S.PtsMaterial) == 72
+    assert C.sizeof(R.PtConfig) == 32 and C.sizeof(R.PtStats) == 112 and C.sizeof(S.PtsMaterial) == 72
     # the cubin inside libpt.so really targets sm_100a
     import subprocess
     out = subprocess.run(["cuobjdump", "-lelf", os.path.join(ROOT, "opengl_ray_tracing_b200", "libpt.so")],

@@ -199,6 +199,20 @@ def test_error_behaviour(R):
     bad = sc.nodes.copy(); leaf = np.where(bad[:, 3] > 0)[0][1]; bad[leaf, 4] = len(sc.tris)
     with pytest.raises(R.PtError, match="leaf range"):
         pt.upload_scene(sc.tris, bad, sc.hdr, sc.hdrCache)
+    # what the production traversal relies on is checked at upload
+    bad = sc.nodes.copy(); bad[leaf, 3] = -1.0
+    with pytest.raises(R.PtError, match="negative triangle count"):
+        pt.upload_scene(sc.tris, bad, sc.hdr, sc.hdrCache)
+    leaves = np.where(sc.nodes[:, 3] > 0)[0]
+    bad = sc.nodes.copy(); bad[leaves[2], 4] = bad[leaves[1], 4]          # two leaves claim the same triangles
+    with pytest.raises(R.PtError, match="two leaves|no leaf"):
+        pt.upload_scene(sc.tris, bad, sc.hdr, sc.hdrCache)
+    inner = np.where(sc.nodes[2:, 3] == 0)[0][0] + 2
+    bad = sc.nodes.copy(); bad[inner, 9:12] -= 0.25 * (bad[inner, 9:12] - bad[inner, 6:9])    # a parent box that no longer holds its children
+    with pytest.raises(R.PtError, match="not inside its parent"):
+        pt.upload_scene(sc.tris, bad, sc.hdr, sc.hdrCache)
+    q = R.PathTracer(32, 16, 2, mode=R.MODE_PARITY_WIDE)               # the reference-topology modes take the array as it is
+    q.upload_scene(sc.tris, bad, sc.hdr, sc.hdrCache); q.close()
     with pytest.raises(R.PtError):
         pt.set_region(0, 0, 33, 16)
     with pytest.raises(R.PtError):

@@ -20,6 +20,7 @@ ap.add_argument("workloads")
 ap.add_argument("--pipeline", type=int, default=2)
 ap.add_argument("--reps", type=int, default=2)
 ap.add_argument("--mode", type=int, default=0)
+ap.add_argument("--env", type=int, default=0, help="1: PT_ENV_CDF_SEARCH (variant 2 only)")
 args = ap.parse_args()
 
 here = os.path.join(ROOT, "opengl_ray_tracing_b200")
@@ -34,8 +35,8 @@ for wl in args.workloads.split():
             continue
         R._lib, R._LIB_PATH = None, path
         try:
-            pt = R.PathTracer(W, H, sc.variant, mode=args.mode, pipeline=args.pipeline)
-            pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache)
+            pt = R.PathTracer(W, H, sc.variant, mode=args.mode, pipeline=args.pipeline, env_sampler=args.env)
+            pt.upload_scene(sc.tris, sc.nodes, sc.hdr, None if args.env else sc.hdrCache)
             pt.set_camera(sc.eye, sc.cam)
             pt.render_spp(0, nf); pt.synchronize()
             out = []
