@@ -41,10 +41,12 @@ namespace pt {
 #define PT_WF_CHUNK 256           // queue entries a warp claims per atomic
 #endif
 #ifndef PT_WF_REFILL_MIN
-#define PT_WF_REFILL_MIN 4        // wf_trace: idle lanes of a warp before it stops to fetch new rays (all idle: always)
+#define PT_WF_REFILL_MIN 16       // wf_trace: free lanes of a warp before it stops to store results and fetch new rays (none busy: always);
+                                  // measured 2 / 4 / 8 / 16 on disney-1M: 7.9 / 8.3 / 8.5 / 8.7 Grays/s
 #endif
 #ifndef PT_WF_TRACE_CTAS
-#define PT_WF_TRACE_CTAS 4        // resident CTAs (256 threads) per SM the traversal kernel is compiled for (4: 64 registers)
+#define PT_WF_TRACE_CTAS 3        // resident CTAs (256 threads) per SM the traversal kernel is compiled for: 3 = 80 registers, no spills;
+                                  // 4 (64 registers, 150 B of spills) -4 %, 5 (48 registers) -10 % on disney-1M
 #endif
 #ifndef PT_WF_SMEM_STACK
 #define PT_WF_SMEM_STACK 0        // wf_trace: traversal-stack entries per thread kept in shared memory (TravStack, pt_trace.cuh)

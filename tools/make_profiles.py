@@ -19,7 +19,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
 G = os.path.join(ROOT, "gpurun_out")
 P = os.path.join(ROOT, "profiles")
-BENCH_CMD = "python bench.py --steps 2 --warmup 1 --no-cpu-baseline"
+BENCH_CMD = "python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-other-workloads"
 ISSUE_PEAK = 148 * 4 * 1.965e9
 
 bench = None
@@ -75,8 +75,9 @@ rd, wr = scaled("dram__bytes_read.sum"), scaled("dram__bytes_write.sum")
 inst = val("smsp__inst_executed.sum")
 samples = spp * cfg["width"] * cfg["height"]
 rays = samples * bench["rays_per_sample"]
-alg = bench["roofline"]["bytes_per_ray"] * rays
-peak = bench["roofline"]["peak"]
+hbm = bench["roofline"].get("hbm", bench["roofline"])          # the byte figure: a sub-object when the issue roofline is primary
+alg = hbm["bytes_per_ray"] * rays
+peak = hbm["peak"]
 stalls = sorted(((val(k), k[len("smsp__average_warps_issue_stalled_"):-len("_per_issue_active.ratio")]) for k in m
                  if k.startswith("smsp__average_warps_issue_stalled") and k.endswith("per_issue_active.ratio") and k.find("selected") < 0), reverse=True)
 summary = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_summary.py"), os.path.join(G, tag + "_render_persistent_raw.csv")],
@@ -100,7 +101,7 @@ with open(os.path.join(P, tag + "_render_persistent.md"), "w") as f:
     f.write("| DRAM | %.2f GB read + %.2f GB write = %.1f GB per launch = %.2f TB/s (%.0f %% of the measured %.2f TB/s) |\n"
             % (rd / 1e9, wr / 1e9, (rd + wr) / 1e9, (rd + wr) / dur / 1e12, 100 * (rd + wr) / dur / 1e9 / peak, peak / 1e3))
     f.write("| algorithmic bytes (bench.py, %.0f B/ray) | %.1f GB per launch -> %.2f TB/s = %.2f of HBM peak; measured DRAM = %.2fx algorithmic |\n"
-            % (bench["roofline"]["bytes_per_ray"], alg / 1e9, alg / dur / 1e12, alg / dur / 1e9 / peak, (rd + wr) / alg))
+            % (hbm["bytes_per_ray"], alg / 1e9, alg / dur / 1e12, alg / dur / 1e9 / peak, (rd + wr) / alg))
     f.write("| L1 hit rate / L2 hit rate | %.1f %% / %.1f %% ; L2 throughput %.0f %% of peak |\n"
             % (val("l1tex__t_sector_hit_rate.pct"), val("lts__t_sector_hit_rate.pct"), val("lts__throughput.avg.pct_of_peak_sustained_elapsed")))
     ll, ls = val("sass__inst_executed_local_loads"), val("sass__inst_executed_local_stores")
@@ -112,17 +113,20 @@ with open(os.path.join(P, tag + "_render_persistent.md"), "w") as f:
 tj_path = os.path.join(P, "traffic.json")
 tj = json.load(open(tj_path)) if os.path.exists(tj_path) else {}
 tj[cfg["workload"]] = {
+    # what bench.py quotes (only when `sass_hash` equals pt_kernel_sass_hash() of the library it runs)
+    "sass_hash": bench.get("kernel_sass_hash"),
+    "frames_per_launch": spp,
     "dram_bytes_per_launch": rd + wr,
+    "warp_instructions_per_launch": int(inst),
+    "threads_per_warp_instruction": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
+    "l2_tex_read_sectors_per_launch": int(val("lts__t_sectors_srcunit_tex_op_read.sum")),
+    "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+    "warps_per_sm": val("sm__warps_active.avg.per_cycle_active"),
+    "l1_hit_pct": val("l1tex__t_sector_hit_rate.pct"),
+    "l1tex_throughput_pct": val("l1tex__throughput.avg.pct_of_peak_sustained_elapsed"),
+    "kernel_ms_under_ncu": dur * 1e3,
     "launch": "render_persistent<CfgFast,2>, %d frames of %dx%d" % (spp, cfg["width"], cfg["height"]),
-    "source": "profiles/%s_render_persistent.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)" % tag,
-    "issue": {
-        "warp_instructions_per_launch": int(inst),
-        "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
-        "warps_per_sm": val("sm__warps_active.avg.per_cycle_active"),
-        "threads_per_warp_instruction": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
-        "issue_peak_warp_instr_per_s": ISSUE_PEAK,
-        "frac_of_issue_peak": inst / dur / ISSUE_PEAK,
-    },
+    "source": "profiles/%s_render_persistent.md (ncu --set full of `%s`)" % (tag, BENCH_CMD),
 }
 json.dump(tj, open(tj_path, "w"), indent=1)
 print(open(os.path.join(P, tag + "_render_persistent.md")).read()[:2600])

@@ -3,7 +3,7 @@
 # Order: the un-profiled command first; then the launch list; then ONE --set full capture of the render kernel.
 cd "$(dirname "$0")/.."
 tag=${1:-r01}; O=gpurun_out
-CMD="python bench.py --steps 2 --warmup 1 --no-cpu-baseline"
+CMD="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-other-workloads"
 $CMD > $O/${tag}_bench_short.json 2> $O/${tag}_bench_short.err || { echo "bench failed"; tail $O/${tag}_bench_short.err; exit 1; }
 tail -c 600 $O/${tag}_bench_short.json
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${tag}_launches.csv $CMD > $O/${tag}_ncu_launches.log 2>&1
