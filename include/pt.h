@@ -117,6 +117,17 @@ int pt_upload_scene(pt_ctx* ctx, const float* tris, int nTriangles, const float*
    hdrCache = NULL. */
 int pt_calculate_hdr_cache(int device, const float* hdr, int width, int height, float* cache);
 
+/* No counterpart in the reference.  pt_calculate_hdr_cache for callers that
+   cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): d_hdr and d_cache are DEVICE
+   pointers the caller owns (height*width*3 floats each, on `device`), the temporaries live in a static 2.1 MB device array
+   inside libpt.so (held by every GPU that loads the library until exit), and the call performs no cudaMalloc / cudaFree / host
+   or library allocation.  Limits: width <= 4096 and width * height <= 262,144 texels (512x512, 1024x256 ...); larger maps are
+   rejected with PT_ERANGE.  Same table bit for bit.  Asynchronous on `cuda_stream` (a cudaStream_t, NULL = the default stream):
+   synchronise that stream before reading d_cache.  All calls on a device share the static array (it keeps the last call's
+   contents; nothing in it needs clearing): calls that overlap on the GPU race — serialise them.  The first call on a device
+   resolves the array's device address (cudaGetSymbolAddress); make that first call outside graph capture. */
+int pt_calculate_hdr_cache_noalloc(int device, const float* d_hdr, int width, int height, float* d_cache, void* cuda_stream);
+
 /* glUniform3fv(eye) + glUniformMatrix4fv(cameraRotate, GL_FALSE) (M:678-679): cameraRotate is column-major. */
 int pt_set_camera(pt_ctx* ctx, const float eye[3], const float cameraRotate[16]);
 

@@ -13,8 +13,10 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <mutex>
+#include <string>
 
-#include "pt_common.cuh"
+#include "pt_internal.h"
 
 namespace pt {
 namespace {
@@ -171,3 +173,60 @@ cudaError_t hdr_cache_device(const float* d_rgb, int W, int H, float4* d_cache4,
 }
 
 }  // namespace pt
+
+// ---- pt_calculate_hdr_cache_noalloc: the same table without a single allocation ------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The temporaries hdr_cache_device()
+// allocates per call (pdf, conditional CDFs, marginal pdf / CDF, lumSum) live in ONE file-scope device array of a fixed,
+// modest size; every GPU that loads libpt.so holds those 2.1 MB until the process exits.
+//   * In host code `g_noalloc_scratch` is only a host-side stand-in for the symbol, NOT a device address: its address is
+//     obtained once per device, with that device current, through cudaGetSymbolAddress, and that pointer is what the
+//     kernels receive.
+//   * Every call on a device shares the array, which keeps the previous call's contents.  Nothing in it has to start at
+//     zero: each kernel below writes every element a later kernel reads (pdf, lumSum, pdf_x, cdf_y, cdf_x are all fully
+//     overwritten for the W x H of the call), so no clearing pass is needed.  Calls that overlap on the GPU (two streams,
+//     two threads) race on the array: serialise them.
+#define PT_NOALLOC_MAX_TEXELS (1 << 18)       // W * H <= 262,144 (512 x 512, 1024 x 256, ...)
+#define PT_NOALLOC_MAX_WIDTH 4096
+#define PT_NOALLOC_FLOATS (2 * PT_NOALLOC_MAX_TEXELS + 2 * PT_NOALLOC_MAX_WIDTH + 64)
+static __device__ __align__(256) float g_noalloc_scratch[PT_NOALLOC_FLOATS];
+
+namespace {
+std::mutex g_noalloc_mutex;
+float* g_noalloc_ptr[64] = {};                // per device: the DEVICE address of g_noalloc_scratch
+}  // namespace
+
+extern "C" int pt_calculate_hdr_cache_noalloc(int device, const float* d_hdr, int width, int height, float* d_cache, void* cuda_stream) {
+    if (!d_hdr || !d_cache || width <= 0 || height <= 0) return fail(PT_EINVAL, "pt_calculate_hdr_cache_noalloc: null buffer or empty image");
+    if (width > PT_NOALLOC_MAX_WIDTH || (long long)width * height > PT_NOALLOC_MAX_TEXELS)
+        return fail(PT_ERANGE, "pt_calculate_hdr_cache_noalloc: " + std::to_string(width) + " x " + std::to_string(height) +
+                               " exceeds the static scratch (width <= " + std::to_string(PT_NOALLOC_MAX_WIDTH) + ", width * height <= " +
+                               std::to_string(PT_NOALLOC_MAX_TEXELS) + "); use pt_calculate_hdr_cache, which allocates");
+    if (device < 0 || device >= 64) return fail(PT_EINVAL, "pt_calculate_hdr_cache_noalloc: device ordinal out of range");
+    CK(cudaSetDevice(device));
+    float* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc_ptr[device]) {                       // set-up, once per device, with that device current
+            void* p = nullptr;
+            CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            g_noalloc_ptr[device] = static_cast<float*>(p);
+        }
+        base = g_noalloc_ptr[device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    const int W = width, H = height;
+    const size_t n = (size_t)W * H;
+    float *pdf = base, *cdf_y = base + PT_NOALLOC_MAX_TEXELS, *pdf_x = base + 2 * PT_NOALLOC_MAX_TEXELS,
+          *cdf_x = pdf_x + PT_NOALLOC_MAX_WIDTH, *lum_sum = cdf_x + PT_NOALLOC_MAX_WIDTH;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    pt::k_luminance<<<blocks, 256, 0, st>>>(d_hdr, n, pdf);
+    pt::k_sequential_sum<<<1, 1024, 0, st>>>(pdf, n, lum_sum);
+    pt::k_normalise<<<blocks, 256, 0, st>>>(pdf, n, lum_sum);
+    pt::k_columns<<<(W + 127) / 128, 128, 0, st>>>(pdf, W, H, pdf_x, cdf_y);
+    pt::k_prefix<<<1, 32, 0, st>>>(pdf_x, W, cdf_x);
+    pt::k_lookup<false><<<blocks, 256, 0, st>>>(pdf, cdf_x, cdf_y, W, H, d_cache);
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+

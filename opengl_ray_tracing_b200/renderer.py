@@ -28,7 +28,7 @@ MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 ENV_TABLE, ENV_CDF_SEARCH = 0, 1
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
-           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_measure_l2_read_gbs", "pt_kernel_sass_hash", "pt_comm_get_unique_id", "pt_comm_init", "pt_comm_info", "pt_comm_destroy", "pt_combine", "pt_last_error",
+           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_calculate_hdr_cache_noalloc", "pt_measure_l2_read_gbs", "pt_kernel_sass_hash", "pt_comm_get_unique_id", "pt_comm_init", "pt_comm_info", "pt_comm_destroy", "pt_combine", "pt_last_error",
            "pt_build_info"]
 
 
@@ -90,6 +90,7 @@ def lib():
         "pt_comm_destroy": (C.c_int, [vp]),
         "pt_combine": (C.c_int, [vp, C.c_int, C.c_uint, vp, vp]),
         "pt_calculate_hdr_cache": (C.c_int, [C.c_int, C.POINTER(C.c_float), C.c_int, C.c_int, C.POINTER(C.c_float)]),
+        "pt_calculate_hdr_cache_noalloc": (C.c_int, [C.c_int, vp, C.c_int, C.c_int, vp, vp]),
         "pt_measure_l2_read_gbs": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     }
     for name, (res, args) in sig.items():
@@ -274,6 +275,12 @@ def measure_l2_read_gbs(device=0, window_mb=48, passes=64):
     l2, hbm = C.c_double(), C.c_double()
     _check(lib().pt_measure_l2_read_gbs(device, window_mb, passes, C.byref(l2), C.byref(hbm)), "pt_measure_l2_read_gbs")
     return l2.value, hbm.value
+
+
+def calculate_hdr_cache_noalloc(d_hdr_ptr, width, height, d_cache_ptr, stream=0, device=0):
+    """pt_calculate_hdr_cache_noalloc: DEVICE pointers in and out (height*width*3 float32 each), static scratch inside libpt.so,
+    no allocation; width <= 4096, width * height <= 262,144.  Asynchronous on `stream`."""
+    _check(lib().pt_calculate_hdr_cache_noalloc(device, d_hdr_ptr, width, height, d_cache_ptr, stream or None), "pt_calculate_hdr_cache_noalloc")
 
 
 def calculate_hdr_cache(hdr, device=0):
