@@ -112,6 +112,16 @@ __global__ void k_gather_tris(const float4* __restrict__ geo, const int* __restr
     geo_fast[4 * (size_t)i + 2] = geo[3 * (size_t)o + 2];
     geo_fast[4 * (size_t)i + 3] = make_float4(__int_as_float(o), __int_as_float(leaf_node[i]), 0.f, 0.f);
 }
+__global__ void k_gather_tris48(const float4* __restrict__ geo, const int* __restrict__ order, const int* __restrict__ leaf_node,
+                                int nTriangles, float4* __restrict__ geo_fast, int2* __restrict__ meta) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nTriangles) return;
+    const int o = order[i];
+    geo_fast[3 * (size_t)i] = geo[3 * (size_t)o];
+    geo_fast[3 * (size_t)i + 1] = geo[3 * (size_t)o + 1];
+    geo_fast[3 * (size_t)i + 2] = geo[3 * (size_t)o + 2];
+    meta[i] = make_int2(o, leaf_node[i]);
+}
 
 __global__ void k_rgb_to_float4(const float* __restrict__ src, size_t n, float4* __restrict__ dst) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -167,8 +177,8 @@ cudaError_t create_events(pt_ctx* c) {
 }
 
 void free_scene(pt_ctx* c) {
-    cudaFree(c->trigeo_fast);
-    c->trigeo_fast = nullptr;
+    cudaFree(c->trigeo_fast); cudaFree(c->trigeo_fast48); cudaFree(c->trimeta);
+    c->trigeo_fast = c->trigeo_fast48 = nullptr; c->trimeta = nullptr;
     cudaFree(c->tris_raw); cudaFree(c->nodes_raw); cudaFree(c->wnodes); cudaFree(c->wnodes_fast); cudaFree(c->trigeo); cudaFree(c->trishade);
     cudaFree(c->materials); cudaFree(c->hdr4); cudaFree(c->cache4); cudaFree(c->light_tab);
     cudaFree(c->env_pdf); cudaFree(c->env_cdf_x); cudaFree(c->env_cdf_y);
@@ -460,6 +470,10 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
         CKU(cudaMalloc(&c->trigeo_fast, (size_t)nTriangles * 4 * sizeof(float4)));
         k_gather_tris<<<(nTriangles + 255) / 256, 256, 0, st>>>(c->trigeo, d_order, d_leaf, nTriangles, c->trigeo_fast);
         CKU(cudaGetLastError());
+        CKU(cudaMalloc(&c->trigeo_fast48, (size_t)nTriangles * 3 * sizeof(float4)));
+        CKU(cudaMalloc(&c->trimeta, (size_t)nTriangles * sizeof(int2)));
+        k_gather_tris48<<<(nTriangles + 255) / 256, 256, 0, st>>>(c->trigeo, d_order, d_leaf, nTriangles, c->trigeo_fast48, c->trimeta);
+        CKU(cudaGetLastError());
         CKU(cudaStreamSynchronize(st));               // ft goes out of scope
     }
     CKU(cudaMalloc(&c->materials, (size_t)nMaterials * 8 * sizeof(float4)));
@@ -494,7 +508,7 @@ int pt_upload_scene(pt_ctx* c, const float* tris, int nTriangles, const float* n
     {
         pt::DevScene& s = c->sc;
         s.tris_raw = c->tris_raw; s.nodes_raw = c->nodes_raw; s.wnodes = c->wnodes; s.wnodes_fast = c->wnodes_fast; s.trigeo = c->trigeo;
-        s.trigeo_fast = c->trigeo_fast;
+        s.trigeo_fast = c->trigeo_fast; s.trigeo_fast48 = c->trigeo_fast48; s.trimeta = c->trimeta;
         s.root_fast = root_fast; c->fast_depth = fast_depth; c->n_fast_inner = nFastInner;
         s.trishade = c->trishade; s.materials = c->materials; s.hdr4 = c->hdr4; s.cache4 = c->cache4;
         s.env_pdf = c->env_pdf; s.env_cdf_x = c->env_cdf_x; s.env_cdf_y = c->env_cdf_y;

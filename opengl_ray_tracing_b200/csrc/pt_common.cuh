@@ -91,7 +91,9 @@ struct DevScene {
     const float4* wnodes;       // nInner x 4 float4 (64 B): child boxes + packed child refs, REFERENCE topology
     const float4* wnodes_fast;  // same record format, binned-SAH topology over the triangles (pt_build.cpp), padded boxes
     const float4* trigeo_fast;  // nTriangles x 4 float4 (64 B), in the order of wnodes_fast's leaves: trigeo's three + (uploaded triangle
-                                // index, reference leaf node holding it, -, -) as int bits: one 64-byte record per triangle test
+                                // index, reference leaf node holding it, -, -) as int bits: one 64-byte record per triangle test (wf_trace)
+    const float4* trigeo_fast48; // the same triangles as 48-byte records (3 float4) + trimeta below: what the persistent / megakernel read
+    const int2* trimeta;        // per re-ordered triangle: (uploaded triangle index, reference leaf node holding it); candidates only
     const float4* trigeo;       // nTriangles x 3 float4 (48 B): (p1,N.x) (p2,N.y) (p3,N.z), N = unit face normal
     const float4* trishade;     // nTriangles x 3 float4 (48 B): (n1, matId) (n2, -) (n3, -)
     const float4* materials;    // nMaterials x 8 float4 (128 B): the 16 parameters, then 16 values derived from them (pt_shade.cuh MaterialD)

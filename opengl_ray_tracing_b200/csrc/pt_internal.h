@@ -47,6 +47,8 @@ struct pt_ctx {
     double build_ms = 0.0;
     float *tris_raw = nullptr, *nodes_raw = nullptr;
     float4 *wnodes = nullptr, *wnodes_fast = nullptr, *trigeo_fast = nullptr, *trigeo = nullptr, *trishade = nullptr, *materials = nullptr, *hdr4 = nullptr, *cache4 = nullptr, *light_tab = nullptr;
+    float4* trigeo_fast48 = nullptr;
+    int2* trimeta = nullptr;
     float *env_pdf = nullptr, *env_cdf_x = nullptr, *env_cdf_y = nullptr;   // PT_ENV_CDF_SEARCH tables
     pt::DevScene sc;
     // camera + region

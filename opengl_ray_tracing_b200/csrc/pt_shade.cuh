@@ -92,7 +92,9 @@ template <class Cfg>
 __device__ __forceinline__ TraceResult trace(const DevScene& sc, V3 o, V3 d, const bool anyhit, Counter<Cfg::COUNT>& cnt, const bool far_origin = false) {
     if (Cfg::RAW) return trace_ref(sc, o, d);         // the reference has no any-hit query: closest hit answers both
     if (Cfg::FAST_TREE) {
+#if PT_FAR_EYE
         if (far_origin) return trace_wide_fallback(sc, o, d);
+#endif
         const uint32_t steps0 = ray_steps(cnt);
         TraceResult tr = trace_fast<PT_STACK>(sc, o, d, anyhit, cnt);
         note_ray(cnt, steps0, sc.ray_histogram);

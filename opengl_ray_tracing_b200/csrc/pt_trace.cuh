@@ -291,6 +291,26 @@ template <> struct Counter<false> {
 #ifndef PT_SMEM_STACK
 #define PT_SMEM_STACK 0
 #endif
+// Triangle records of trace_fast (the persistent kernel and the megakernel): PT_TRI64 = 0: 48-byte records (three 16-byte loads)
+// + the (index, leaf) pair fetched only for the 0.25 candidates per ray; 1: the 64-byte records wf_trace reads (two LDG.E.256).
+// The 64-byte form costs these kernels 33 % more triangle bytes through an L1 that already misses half of the time:
+// is-1M 21.3 vs 22.0 Grays/s in the same box (round-1 build as the yardstick), so they keep the 48-byte form.
+// trace_fast's stack when nothing of it lives in shared memory or a register: a plain local array and an int, written out —
+// NOT the TravStack template with SMEM = 0, although that is the same program: ptxas lays the loop out differently and the
+// persistent kernel loses 1.3 % on is-1M (47.41 vs 46.84 ms per 256-frame launch, same box, tools/r02_call11.sh).  "Code shape
+// is worth per cents" (DESIGN.md section 9).
+#ifndef PT_PLAIN_STACK
+#define PT_PLAIN_STACK (PT_SMEM_STACK == 0 && !PT_STACK_TOS)
+#endif
+#ifndef PT_TRI64
+#define PT_TRI64 0
+#endif
+#ifndef PT_NODE256
+#define PT_NODE256 0                  // trace_fast: wide nodes by two 32-byte loads (1) or four 16-byte loads (0): 0 is +0.4 % here (wf_trace: 256-bit, +4 %)
+#endif
+#ifndef PT_FAR_EYE
+#define PT_FAR_EYE 1                  // primary rays of an eye beyond 8 scene radii take the reference topology (pt_shade.cuh trace<>)
+#endif
 #ifndef PT_STACK_TOS
 #define PT_STACK_TOS 0
 #endif
@@ -362,14 +382,24 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
 #else
     uint32_t* const smem_base = nullptr;
 #endif
+#if PT_PLAIN_STACK
+    uint32_t stack_ref[STACK];                        // the round-1 form, verbatim: a plain local array and an int
+    int sp = 0;
+    (void)smem_base;
+#else
     TravStack<STACK, PT_SMEM_STACK> stk;
     stk.init(smem_base);
+#endif
     uint32_t ref = sc.root_fast;
     while (true) {
         while (ref_count(ref) == 0) {                 // inner node: both child boxes and refs in one 64-byte record
             const float4* w = sc.wnodes_fast + 4 * (size_t)PT_IDX(sc, ref, sc.nFastInner);
+#if PT_NODE256
             float4 q0, q1, q2, q3;
             ldg8(w, q0, q1); ldg8(w + 2, q2, q3);
+#else
+            const float4 q0 = ldg4(w), q1 = ldg4(w + 1), q2 = ldg4(w + 2), q3 = ldg4(w + 3);
+#endif
             cnt.inner();
             float e1, e2;
             const bool g1 = slab_cull_fused(cr, mk3(q0.x, q0.y, q0.z), mk3(q0.w, q1.x, q1.y), cull, e1);
@@ -377,8 +407,13 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
             const uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
             if (g1 && g2) {
                 const bool left_first = e1 <= e2;
+#if PT_PLAIN_STACK
+                if (sp >= STACK) { *sc.error_flag = PT_ERR_STACK; return res; }
+                stack_ref[sp++] = left_first ? rref : lref;
+#else
                 if (stk.full()) { *sc.error_flag = PT_ERR_STACK; return res; }
                 stk.push(left_first ? rref : lref);
+#endif
                 ref = left_first ? lref : rref;
             } else if (g1 || g2) {
                 ref = g1 ? lref : rref;
@@ -389,15 +424,24 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
         if (ref != PT_REF_NONE) {                     // leaf: hitArray over its (re-ordered) triangles
             const uint32_t first = ref_index(ref), end = first + ref_count(ref);
             for (uint32_t i = first; i < end; i++) {
+#if PT_TRI64
                 const float4* g = sc.trigeo_fast + 4 * (size_t)PT_IDX(sc, i, sc.nTriangles);
                 float4 a, b, c, m4;
                 ldg8(g, a, b); ldg8(g + 2, c, m4);
+#else
+                const float4* g = sc.trigeo_fast48 + 3 * (size_t)PT_IDX(sc, i, sc.nTriangles);
+                const float4 a = ldg4(g), b = ldg4(g + 1), c = ldg4(g + 2);
+#endif
                 cnt.tri();
                 float tt; bool ins;
                 if (hit_triangle(r, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), mk3(a.w, b.w, c.w), res.t, tt, ins,
                                  !anyhit && res.tri >= 0)) {
                     cnt.cand();
+#if PT_TRI64
                     const int2 meta = make_int2(__float_as_int(m4.x), __float_as_int(m4.y));
+#else
+                    const int2 meta = __ldg(sc.trimeta + i);
+#endif
                     if (meta.y != 1) {                // the reference never box-tests its root (P:342-343)
                         const float* nd = sc.nodes_raw + 12 * (size_t)PT_IDX(sc, meta.y, sc.nNodes);
                         float e;
@@ -406,13 +450,22 @@ __device__ __forceinline__ TraceResult trace_fast(const DevScene& sc, V3 origin,
                     }
                     if (!anyhit && tt == res.t) { tie = true; continue; }
                     res.t = tt; res.tri = meta.x; res.inside = ins;
+#if PT_PLAIN_STACK
+                    if (anyhit) { sp = 0; break; }    // a shadow ray needs no more than this
+#else
                     if (anyhit) { stk.clear(); break; }   // a shadow ray needs no more than this
+#endif
                     cull = s_mul(tt, PT_CULL_SLACK);
                 }
             }
         }
-        if (stk.empty()) break;                       // the ONE pop site (after a leaf, and after a node whose children both missed)
-        ref = stk.pop();                              // and the one exit: this lane's ray is finished when nothing is deferred
+#if PT_PLAIN_STACK
+        if (sp == 0) break;                           // the ONE pop site (after a leaf, and after a node whose children both missed)
+        ref = stack_ref[--sp];                        // and the one exit: this lane's ray is finished when nothing is deferred
+#else
+        if (stk.empty()) break;
+        ref = stk.pop();
+#endif
     }
     if (!anyhit && tie) res.tri = -2;                 // caller: re-trace on the reference topology
     return res;
