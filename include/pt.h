@@ -165,6 +165,11 @@ int pt_clear(pt_ctx* ctx);
 
 /* New (the reference never reads pixels back): W*H float4, row 0 = bottom row (GL window origin). Synchronises. */
 int pt_readback(pt_ctx* ctx, float* rgba, size_t bytes);
+/* pt_readback without the wait: snapshots the framebuffer as of this call (device-to-device, stream-ordered) and copies the
+   snapshot to `rgba_pinned` (pinned host memory) on a second stream, so that the next pt_render_spp overlaps the transfer.
+   The buffer is valid after pt_synchronize(ctx).  One copy in flight per context: a second call waits (on the device) for
+   the first.  No reference equivalent. */
+int pt_readback_async(pt_ctx* ctx, float* rgba_pinned, size_t bytes);
 /* pass3.draw() (M:706): the display pass pass3.fsh:14-24 — toneMapping(colour, 1.5) — fused with the window's 8-bit
    conversion on the device; W*H RGBA8, row 0 = TOP row (image order), alpha 255.  A quarter of pt_readback's bytes
    cross PCIe.  Synchronises. */
@@ -209,6 +214,8 @@ int pt_comm_destroy(pt_ctx* ctx);
 #define PT_COMBINE_SUM      0
 #define PT_COMBINE_DISJOINT 1
 #define PT_COMBINE_DISPLAY  4
+#define PT_COMBINE_ASYNC    8   /* rank 0's host copy rides on a second stream and overlaps whatever the context renders next; the host
+                                   buffers (pinned memory, or the copy is not asynchronous) are valid after pt_synchronize(ctx) */
 int pt_combine(pt_ctx* ctx, int flags, unsigned total_frames, float* rgba_host, unsigned char* rgba8_host);
 
 int pt_synchronize(pt_ctx* ctx);

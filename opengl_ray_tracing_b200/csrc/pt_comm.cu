@@ -259,9 +259,9 @@ int pt_comm_info(pt_ctx* c, int* world, int* rank, int* peer_memory) {
 int pt_combine(pt_ctx* c, int flags, unsigned total_frames, float* rgba_host, unsigned char* rgba8_host) {
     if (!c) return fail(PT_EINVAL, "pt_combine: null context");
     const int kind = flags & 3;
-    const bool display = (flags & PT_COMBINE_DISPLAY) != 0;
-    if ((flags & ~(3 | PT_COMBINE_DISPLAY)) || (kind != PT_COMBINE_SUM && kind != PT_COMBINE_DISJOINT))
-        return fail(PT_EINVAL, "pt_combine: flags = PT_COMBINE_SUM or PT_COMBINE_DISJOINT, optionally | PT_COMBINE_DISPLAY");
+    const bool display = (flags & PT_COMBINE_DISPLAY) != 0, async = (flags & PT_COMBINE_ASYNC) != 0;
+    if ((flags & ~(3 | PT_COMBINE_DISPLAY | PT_COMBINE_ASYNC)) || (kind != PT_COMBINE_SUM && kind != PT_COMBINE_DISJOINT))
+        return fail(PT_EINVAL, "pt_combine: flags = PT_COMBINE_SUM or PT_COMBINE_DISJOINT, optionally | PT_COMBINE_DISPLAY | PT_COMBINE_ASYNC");
     if (kind == PT_COMBINE_SUM && total_frames == 0) return fail(PT_EINVAL, "pt_combine: total_frames must be > 0 for PT_COMBINE_SUM");
     if (rgba8_host && !display) return fail(PT_EINVAL, "pt_combine: rgba8_host needs PT_COMBINE_DISPLAY (on every rank)");
     CK(cudaSetDevice(c->cfg.device));
@@ -273,6 +273,9 @@ int pt_combine(pt_ctx* c, int flags, unsigned total_frames, float* rgba_host, un
     if (!m) return fail(PT_EINVAL, "pt_combine: pt_comm_init first (world = 1 is allowed)");
     if (m->rank != 0 && (rgba_host || rgba8_host)) return fail(PT_EINVAL, "pt_combine: only rank 0 receives the image");
     const int grid = (c->num_sms > 0 ? c->num_sms : 148) * 4;
+    // an asynchronous host copy of the PREVIOUS combined image may still read rank 0's output images: the kernels that
+    // overwrite them (on every rank) come after barrier A, which rank 0 joins only once that copy is done
+    if (m->rank == 0 && c->copy_pending) CK(cudaStreamWaitEvent(c->stream, c->ev_copied, 0));
     if (m->world == 1) {
         // one GPU: the same consumer epilogue over the context's own framebuffer
         PeerTable t; std::memset(&t, 0, sizeof t); t.fb[0] = c->accum;
@@ -298,6 +301,15 @@ int pt_combine(pt_ctx* c, int flags, unsigned total_frames, float* rgba_host, un
         }
     }
     if (m->rank == 0 && (rgba_host || rgba8_host)) {
+        if (async) {
+            // the copy rides on the context's copy stream and overlaps the next step's rendering; pt_synchronize waits for it
+            int rc = pt_copy_setup(c);
+            if (rc != PT_OK) return rc;
+            bool first = true;
+            if (rgba_host) { rc = pt_copy_enqueue(c, rgba_host, m->my_f4, npx * sizeof(float4), first); first = false; if (rc != PT_OK) return rc; }
+            if (rgba8_host) { rc = pt_copy_enqueue(c, rgba8_host, m->my_u8, npx * 4, first); if (rc != PT_OK) return rc; }
+            return PT_OK;
+        }
         if (rgba_host) CK(cudaMemcpyAsync(rgba_host, m->my_f4, npx * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
         if (rgba8_host) CK(cudaMemcpyAsync(rgba8_host, m->my_u8, npx * 4, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaStreamSynchronize(c->stream));

@@ -171,6 +171,8 @@ struct RenderParams {
     unsigned long long* work_counters;   // [4]: inner nodes fetched, triangles tested, leaf-box candidates, - (PT_MODE_FAST_COUNT)
     WaveBuffers wf;             // PT_PIPELINE_WAVEFRONT only
     uint32_t sched_stride;      // PT_PIPELINE_PERSISTENT: tile rows are visited in this many interleaved passes (0: the kernel's rule)
+    const uint32_t* tile_tab;   // PT_PIPELINE_PERSISTENT: [owned tiles] the k-th tile of a frame in visiting order, tx | strip << 16
+                                // (written per launch by tile_order_kernel), or null: every warp derives it per item
     const float* sobol_tab;     // variant 2: [n_frames][8] Sobol coordinates of this launch's frames (written by sobol_table_kernel) or null
     uint32_t* sched;            // PT_PIPELINE_PERSISTENT: [0] work head (the next frame a pixel accepts travels in the pixel's own .w)
     unsigned* cost;             // optional W*H cost map (SM cycles spent on the pixel by the last launch) or null

@@ -18,6 +18,8 @@ int pt_fail(int code, const std::string& msg);          // records the thread-lo
 
 struct PtComm;                                           // pt_comm.cu: multi-GPU state of a context
 void pt_comm_release(struct pt_ctx* c);                  // called by pt_destroy
+extern "C" int pt_copy_setup(struct pt_ctx* c);          // pt_api.cu (internal, not in pt.h): creates the copy stream + events on first use
+extern "C" int pt_copy_enqueue(struct pt_ctx* c, void* host, const void* dev, size_t bytes, bool first);   // D2H on the copy stream, after ev_image
 
 struct pt_ctx {
     PtConfig cfg;
@@ -36,6 +38,8 @@ struct pt_ctx {
     pt::WaveBuffers wf;          // wavefront path state, allocated at the first wavefront render
     void* wf_block = nullptr;
     uint32_t* sched = nullptr;   // persistent pipeline: work head
+    uint32_t* tile_tab = nullptr;   // persistent pipeline: visiting order of a frame's tiles (RenderParams.tile_tab)
+    size_t tile_cap = 0;
     float* sobol_tab = nullptr;  // variant 2: Sobol coordinates of the frames of one launch, [sobol_cap][8]
     size_t sobol_cap = 0;
     uchar4* display = nullptr;   // pt_readback_display staging
@@ -61,5 +65,11 @@ struct pt_ctx {
     double render_ms = 0.0;
     unsigned long long wf_waves = 0, wf_retries = 0;   // wavefront pipeline: waves rendered / repeated since the last reset
     PtComm* comm = nullptr;      // pt_comm_init
+    // asynchronous host copies (pt_readback_async, pt_combine | PT_COMBINE_ASYNC): a second stream carries the device-to-host
+    // copy of a finished image while the context's stream already renders the next step
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_image = nullptr, ev_copied = nullptr;
+    bool copy_pending = false;
+    float4* snapshot = nullptr;  // pt_readback_async: the framebuffer as of the call (the next render overwrites accum)
 };
 

@@ -14,6 +14,8 @@
 // path (primary and bounce rays) goes through ONE traversal site inside a loop, and shadow rays through a
 // second, any-hit site.  What must survive a traversal is kept small: f_r, N·L, pdf, history, Lo.
 #pragma once
+#include <algorithm>
+
 #include "pt_trace.cuh"
 #include "../../include/ptmath.h"
 
@@ -833,6 +835,30 @@ __device__ __forceinline__ void st_relaxed_v4(float4* p, float x, float y, float
 #ifndef PT_PERSIST_MIN_CTAS
 #define PT_PERSIST_MIN_CTAS 5           // measured on B200 (is-1M / lambert-100k / disney-1M, Grays/s): 3 CTAs 11.6/5.7/5.3, 4: 12.4/6.5/6.1, 6: 12.6/7.0/6.8, 8: 12.1/6.9/6.7
 #endif
+// the t0-th tile of a frame in visiting order (S interleaved passes over the tile rows, see render_persistent) -> (tx, strip)
+__device__ __forceinline__ void persist_tile(const TileMap& tm, uint32_t S, uint32_t t0, int& tx, int& strip) {
+    const uint32_t row0 = t0 / (uint32_t)tm.per_row, j0 = t0 - row0 * (uint32_t)tm.per_row;
+    const uint32_t R = (uint32_t)tm.rows, q = R / S, rem = R - q * S;
+    uint32_t a, k;
+    if (row0 < rem * (q + 1)) { a = row0 / (q + 1); k = row0 - a * (q + 1); }
+    else { const uint32_t i2 = row0 - rem * (q + 1); a = rem + i2 / q; k = i2 - (a - rem) * q; }
+    const uint32_t tile = (a + k * S) * (uint32_t)tm.per_row + j0;
+    tm.locate(tile, tx, strip);
+}
+// That mapping costs seven 32-bit integer divisions (~120 warp instructions) per work item, 5 % of ALL instructions the kernel
+// executes on the metric scene (2,490 per item on average, ~500 for a sky tile), and it is the same for every frame: one
+// small launch tabulates it (PT_TILE_TAB), the render kernel reads 4 bytes per item.
+#ifndef PT_TILE_TAB
+#define PT_TILE_TAB 1
+#endif
+static __global__ void tile_order_kernel(const TileMap tm, uint32_t S, uint32_t ntiles, uint32_t* __restrict__ tab) {
+    const uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t0 >= ntiles) return;
+    int tx, strip;
+    persist_tile(tm, S, t0, tx, strip);
+    tab[t0] = (uint32_t)tx | ((uint32_t)strip << 16);
+}
+
 template <class Cfg, int VARIANT>
 __global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) render_persistent(const __grid_constant__ RenderParams p) {
     const int lane = threadIdx.x & 31;
@@ -862,14 +888,13 @@ __global__ void __launch_bounds__(PT_PERSIST_THREADS, PT_PERSIST_MIN_CTAS) rende
 #pragma unroll 1
         for (uint32_t item = first_item; item < first_item + PT_PERSIST_CHUNK && item < nitems; item++) {
             const uint32_t f = item / ntiles, t0 = item - f * ntiles;
-            const uint32_t row0 = t0 / (uint32_t)tm.per_row, j0 = t0 - row0 * (uint32_t)tm.per_row;
-            const uint32_t R = (uint32_t)tm.rows, q = R / S, rem = R - q * S;
-            uint32_t a, k;
-            if (row0 < rem * (q + 1)) { a = row0 / (q + 1); k = row0 - a * (q + 1); }
-            else { const uint32_t i2 = row0 - rem * (q + 1); a = rem + i2 / q; k = i2 - (a - rem) * q; }
-            const uint32_t tile = (a + k * S) * (uint32_t)tm.per_row + j0;
             int tx, strip;
-            tm.locate(tile, tx, strip);
+            if (PT_TILE_TAB && p.tile_tab != nullptr) {
+                const uint32_t packed = __ldg(p.tile_tab + t0);
+                tx = (int)(packed & 0xffffu); strip = (int)(packed >> 16);
+            } else {
+                persist_tile(tm, S, t0, tx, strip);
+            }
             const int px = p.x0 + tx * 8 + (lane & 7);
             const int py = p.y0 + strip * 4 + (lane >> 3);
             const bool valid = px < p.x1 && py < p.y1;
@@ -943,6 +968,13 @@ cudaError_t launch_persistent_variant(const RenderParams& p, int num_sms, cudaSt
     int grid = num_sms * (per_sm > 0 ? per_sm : 1);
     const int need = (int)((ntiles + PT_PERSIST_THREADS / 32 - 1) / (PT_PERSIST_THREADS / 32));
     if (grid > need) grid = need;
+    if (PT_TILE_TAB && p.tile_tab != nullptr) {
+        // the visiting order of a frame's tiles, tabulated with the kernel's own rule for S (which depends on this grid)
+        uint32_t S = p.sched_stride;
+        if (S == 0u) S = VARIANT == 2 ? std::max(1u, (uint32_t)(0.74f * (float)ntiles / (float)((uint32_t)grid * (PT_PERSIST_THREADS / 32u)) + 0.5f)) : 1u;
+        S = std::min(S, std::max(1u, (uint32_t)tm.rows));
+        tile_order_kernel<<<(unsigned)((ntiles + 255) / 256), 256, 0, stream>>>(tm, S, (uint32_t)ntiles, const_cast<uint32_t*>(p.tile_tab));
+    }
     kern<<<grid, PT_PERSIST_THREADS, 0, stream>>>(p);
     return cudaGetLastError();
 }

@@ -22,12 +22,12 @@ MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE, MODE_PARITY_FAST, MODE_FAST_COUNT 
 DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 
 ACC_MEAN, ACC_SUM = 0, 1
-COMBINE_SUM, COMBINE_DISJOINT, COMBINE_DISPLAY = 0, 1, 4
+COMBINE_SUM, COMBINE_DISJOINT, COMBINE_DISPLAY, COMBINE_ASYNC = 0, 1, 4, 8
 COMM_ID_BYTES = 128
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 ENV_TABLE, ENV_CDF_SEARCH = 0, 1
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
-           "pt_clear", "pt_readback", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
+           "pt_clear", "pt_readback", "pt_readback_async", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
            "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_calculate_hdr_cache_noalloc", "pt_measure_l2_read_gbs", "pt_kernel_sass_hash", "pt_comm_get_unique_id", "pt_comm_init", "pt_comm_info", "pt_comm_destroy", "pt_combine", "pt_last_error",
            "pt_build_info"]
 
@@ -70,6 +70,7 @@ def lib():
         "pt_render_frames": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_int]),
         "pt_clear": (C.c_int, [vp]),
         "pt_readback": (C.c_int, [vp, vp, C.c_size_t]),
+        "pt_readback_async": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_readback_primary_ids": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_readback_display": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_enable_cost_map": (C.c_int, [vp, C.c_int]),
@@ -180,6 +181,10 @@ class PathTracer:
 
     def readback_into(self, host_ptr, nbytes):
         _check(lib().pt_readback(self._h, host_ptr, nbytes), "pt_readback")
+
+    def readback_async(self, host_ptr, nbytes):
+        """pt_readback_async: snapshot now, copy on a second stream; the (pinned) buffer is valid after synchronize()."""
+        _check(lib().pt_readback_async(self._h, host_ptr, nbytes), "pt_readback_async")
 
     def readback_display(self) -> np.ndarray:
         """pass3.fsh tone map + 8-bit conversion on the device: uint8 [H, W, 4], row 0 = top row."""

@@ -330,6 +330,31 @@ def test_wavefront_waves_and_lane_refill(R, monkeypatch):
         assert img.tobytes() == ref.tobytes() and (ids == ids_ref).all() and st["rays"] == st_ref["rays"]
 
 
+def test_readback_async_is_a_snapshot(R):
+    """pt_readback_async copies the image AS OF THE CALL while later launches already overwrite the framebuffer."""
+    import torch
+    sc = small_scene("is", "10k", hdr_res=(256, 128))
+    W, H = 256, 144
+    pt = R.PathTracer(W, H, sc.variant, mode=R.MODE_FAST)
+    pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); pt.set_camera(sc.eye, sc.cam)
+    pt.render_spp(0, 4)
+    want4 = pt.readback().copy()
+    pt.clear()
+    host = [torch.empty((H, W, 4), dtype=torch.float32).pin_memory() for _ in range(2)]
+    pt.render_spp(0, 4)
+    pt.readback_async(host[0].data_ptr(), host[0].numel() * 4)
+    pt.render_spp(4, 60)                                       # overwrites the framebuffer while the copy may still run
+    pt.readback_async(host[1].data_ptr(), host[1].numel() * 4)   # a second copy queues behind the first
+    pt.render_spp(64, 8)
+    pt.synchronize()
+    assert host[0].numpy().tobytes() == want4.tobytes()
+    pt2 = R.PathTracer(W, H, sc.variant, mode=R.MODE_FAST)
+    pt2.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); pt2.set_camera(sc.eye, sc.cam)
+    pt2.render_spp(0, 64)
+    assert host[1].numpy().tobytes() == pt2.readback().tobytes()
+    pt2.close(); pt.close()
+
+
 def test_counting_build_and_cost_map(R):
     sc = small_scene("is", "10k", hdr_res=(256, 128))
     W, H, NF = 128, 72, 2

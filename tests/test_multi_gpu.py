@@ -20,7 +20,7 @@ def R():
     return renderer
 
 
-def run_ranks(R, sc, W, H, NF, world, split):
+def run_ranks(R, sc, W, H, NF, world, split, overlap=False):
     uid = R.comm_unique_id()
     out, errs = {}, []
 
@@ -34,7 +34,20 @@ def run_ranks(R, sc, W, H, NF, world, split):
             if split == "tile":
                 pt.set_tile_interleave(world, rank)
                 pt.render_spp(0, NF)
-                res = pt.combine_readback(R.COMBINE_DISJOINT, NF, display=True)
+                if overlap and rank == 0:          # PT_COMBINE_ASYNC: the copy lands at synchronize(), rendering goes on meanwhile
+                    import torch
+                    hf = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+                    hd = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+                    pt.combine(R.COMBINE_DISJOINT | R.COMBINE_DISPLAY | R.COMBINE_ASYNC, NF, hf.data_ptr(), hd.data_ptr())
+                    pt.render_spp(NF, 4)
+                    pt.synchronize()
+                    res = (hf.numpy().copy(), hd.numpy().copy())
+                elif overlap:
+                    pt.combine(R.COMBINE_DISJOINT | R.COMBINE_DISPLAY | R.COMBINE_ASYNC, NF)
+                    pt.render_spp(NF, 4)
+                    res = None
+                else:
+                    res = pt.combine_readback(R.COMBINE_DISJOINT, NF, display=True)
             else:
                 n = (NF - rank + world - 1) // world
                 pt.render_frames(rank, n, world, R.ACC_SUM)
@@ -67,6 +80,8 @@ def test_combine_tile_and_sample_split(R):
     assert t["info"]["world"] == 2
     assert t["img"].tobytes() == ref.tobytes(), "tile split + pt_combine must be bit-identical to one GPU"
     assert t["disp"].tobytes() == ref_disp.tobytes()
+    t = run_ranks(R, sc, W, H, NF, 2, "tile", overlap=True)
+    assert t["img"].tobytes() == ref.tobytes() and t["disp"].tobytes() == ref_disp.tobytes(), "PT_COMBINE_ASYNC"
     s = run_ranks(R, sc, W, H, NF, 2, "sample")
     assert rrmse(s["img"], ref) <= 1e-5 and (s["img"][..., 3] == 1.0).all()
     assert (np.abs(s["disp"].astype(int) - ref_disp.astype(int)) <= 1).all()
