@@ -530,6 +530,12 @@ def run_ours(args):
             hbm_obj.update({"kernel": "render_persistent<CfgFast,%d>" % sc.variant, "kernel_ms_per_launch": kernel_s * 1e3,
                             "l2_peak_gbs": l2_gbs, "no_issue_figure": cap_src})
             line["roofline"] = hbm_obj
+        # what the traversal itself requests (before any cache): 64 B per inner node visited, 48 B per triangle tested
+        node_gbs = rays_per_launch * cs["inner_visits"] / max(1, cs["rays"]) * 64.0 / kernel_s / 1e9
+        tri_gbs = rays_per_launch * cs["tri_tests"] / max(1, cs["rays"]) * 48.0 / kernel_s / 1e9
+        line["roofline"]["fetches"] = {"node_gbs": node_gbs, "triangle_gbs": tri_gbs, "unit": "GB/s requested by the traversal loop",
+                                       "of_l2_read_peak": (node_gbs + tri_gbs) / l2_gbs, "of_hbm_peak": (node_gbs + tri_gbs) / peak,
+                                       "note": "an upper bound of what reaches L2: about half of these requests hit L1 (capture)"}
         line["roofline"]["l2_read_peak_gbs"] = l2_gbs
         line["roofline"]["hbm_read_probe_gbs"] = hbm_probe_gbs
         line["parity"] = parity
