@@ -67,6 +67,10 @@ def parse_args():
                     help="N > 1: sample = frames dealt round-robin, per-rank sums combined and scaled (default: every rank keeps the "
                          "whole image, so a tile's consecutive frames stay ~11 resident-warp generations apart, as on one GPU); "
                          "tile = diagonal 8x4 tiles, bit-identical to one GPU")
+    ap.add_argument("--combine", default="pipelined", choices=["pipelined", "sync"],
+                    help="N > 1 with peer memory: pipelined = PT_COMBINE_PIPELINED (the combine of step k runs on a second stream under "
+                         "the rendering of step k + 1; the timed region is then ONE event pair around all K steps, L2 flushes "
+                         "included); sync = two NCCL barriers and the combine kernel on the render stream in every step")
     ap.add_argument("--mode", type=int, default=0, help="0 fast (production), 1 parity-ref, 2 parity-wide")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-l2-flush", action="store_true")
@@ -343,6 +347,7 @@ def run_ours(args):
     tile, samp = D.TilePlan(W, H, world, rank), D.SamplePlan(world, rank)
     spp = args.spp
     kind = R.COMBINE_DISJOINT if args.split == "tile" else R.COMBINE_SUM
+    pipelined = world > 1 and bool(peer) and args.combine == "pipelined"
 
     def render_step(first, host_ptr=None, overlap=False):
         """One step: this rank's share of frames first .. first+spp-1, then (N > 1) the combine onto rank 0.
@@ -355,7 +360,8 @@ def run_ours(args):
             D.render_tiles(pt, tile, first, spp)
         else:
             D.render_samples(pt, samp, first, spp)           # per-rank sums of ALL frames so far (PT_ACC_SUM)
-        pt.combine(kind | (R.COMBINE_ASYNC if overlap else 0), first + spp, host_ptr if rank == 0 else None, None)
+        how = R.COMBINE_PIPELINED if pipelined else (R.COMBINE_ASYNC if overlap else 0)
+        pt.combine(kind | how, first + spp, host_ptr if rank == 0 else None, None)
 
     def barrier():
         pt.synchronize()
@@ -373,8 +379,10 @@ def run_ours(args):
     sampler = ClockSampler(local)
     sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ev_all = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
     barrier()
     t_wall0 = time.perf_counter()
+    ev_all[0].record(stream)
     for k in range(args.steps):
         if flush is not None:
             with torch.cuda.stream(stream):
@@ -382,11 +390,18 @@ def run_ours(args):
         ev[k][0].record(stream)
         render_step(frame); frame += spp
         ev[k][1].record(stream)
+    if pipelined:
+        pt.combine_fence()                            # the render stream waits for the last combine, on every rank
+    ev_all[1].record(stream)
     barrier()
     t_wall = time.perf_counter() - t_wall0
     clocks = sampler.stop()
     st = pt.stats()
-    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    # sync combine / one GPU: the per-step event pairs (the L2 flushes lie between them).  Pipelined combine: the combine of
+    # step k runs beside the flush and the render of step k + 1, so only ONE pair around the whole loop — flushes included,
+    # closed after the fence — counts everything
+    dev_ms = ev_all[0].elapsed_time(ev_all[1]) if pipelined else sum(a.elapsed_time(b) for a, b in ev)
+    render_stream_ms = sum(a.elapsed_time(b) for a, b in ev) / args.steps
     tot = torch.tensor([dev_ms, float(st["rays"]), float(st["samples"]), float(st["launches"]), float(st["render_ms"]),
                         float(clocks["sm_mhz"] or 0.0), float(len(clocks["reasons"]))],
                        dtype=torch.float64, device="cuda")
@@ -471,7 +486,11 @@ def run_ours(args):
                        "max_bounce": sc.max_bounce, "width": W, "height": H, "spp_per_step": spp, "mode": args.mode,
                        "pipeline": {0: "megakernel", 1: "wavefront", 2: "persistent"}[args.pipeline],
                        "split": args.split if world > 1 else "none",
-                       "combine": ("pt_combine: one kernel per GPU over NVLink peer memory" if peer else "pt_combine: ncclReduce + consume kernel (no peer memory)") if world > 1 else "none",
+                       "combine": (("pt_combine | PT_COMBINE_PIPELINED: snapshot + flag on the render stream, one small kernel per GPU on a second stream "
+                                    "(in-kernel flag waits over NVLink peer memory) under the next step's render; timed as ONE event pair around "
+                                    "all steps incl. the L2 flushes" if pipelined else
+                                    "pt_combine: one kernel per GPU over NVLink peer memory between two NCCL barriers") if peer
+                                   else "pt_combine: ncclReduce + consume kernel (no peer memory)") if world > 1 else "none",
                        "hdr": "synthHdr(%d, %d, seed 1) — the reference's .hdr files are not on the GPU box" % (sc.hdr.shape[1], sc.hdr.shape[0]),
                        "l2": "flushed between steps (256 MiB fill)" if flush is not None else "not flushed",
                        "scene_bytes_hbm": int(sc.tris.nbytes + sc.nodes.nbytes + sc.nTriangles * 96 + st["n_inner_nodes"] * 64
@@ -483,6 +502,7 @@ def run_ours(args):
             "gpu_launches": int(launches), "clocks": clocks,
             "scene_build_s": t_scene, "scene_upload_s": t_upload, "wall_s_timed_region": t_wall,
             "kernel_ms_per_step": kern_ms / args.steps, "per_rank_kernel_ms": per_rank_kernel_ms,
+            "render_stream_ms_per_step_rank0": render_stream_ms,
             "kernel_sass_hash": R.kernel_sass_hash(),
         }
         # ---- roofline of the render kernel ----

@@ -216,7 +216,20 @@ int pt_comm_destroy(pt_ctx* ctx);
 #define PT_COMBINE_DISPLAY  4
 #define PT_COMBINE_ASYNC    8   /* rank 0's host copy rides on a second stream and overlaps whatever the context renders next; the host
                                    buffers (pinned memory, or the copy is not asynchronous) are valid after pt_synchronize(ctx) */
+#define PT_COMBINE_PIPELINED 16 /* the whole combine leaves the render stream (needs peer memory and world > 1; otherwise the flag is ignored
+                                   and the call behaves as without it, plus PT_COMBINE_ASYNC): the call snapshots this rank's framebuffer
+                                   (device to device, two alternating slots), announces it to the peers with a flag store over NVLink and
+                                   returns; a second stream runs ONE small kernel that waits for every rank's announcement inside the kernel
+                                   (no NCCL kernel, no host), reduces this rank's slice of the snapshots and announces completion; rank 0
+                                   then copies the image to rgba_host / rgba8_host (pinned).  That kernel fits beside the resident render
+                                   kernel on every SM, so the combine of step k runs under the rendering of step k + 1 and a rank's render
+                                   stream waits for a peer only when that peer is two combines behind.  Same bits as the synchronous
+                                   combine.  The host buffers are valid after pt_synchronize(ctx); every rank must pt_synchronize (and the
+                                   ranks must meet, e.g. in a barrier of the host's) before any of them is destroyed. */
 int pt_combine(pt_ctx* ctx, int flags, unsigned total_frames, float* rgba_host, unsigned char* rgba8_host);
+/* Makes the context's render stream wait (on the device, not the host) until every rank's slice of every pipelined combine
+   issued so far has landed in rank 0's image.  Collective in the sense that all ranks must have issued those combines. */
+int pt_combine_fence(pt_ctx* ctx);
 
 int pt_synchronize(pt_ctx* ctx);
 int pt_get_stats(pt_ctx* ctx, PtStats* out);

@@ -871,13 +871,21 @@ int pt_synchronize(pt_ctx* c) {
         CK(cudaStreamSynchronize(c->copy_stream));
         c->copy_pending = false;
     }
+    if (c->comm) {
+        const int rc = pt_comm_check(c);
+        if (rc != PT_OK) return rc;
+    }
     return collect_timing(c);
 }
 
 // ---- asynchronous host copies -------------------------------------------------------------------------------------------
 int pt_copy_setup(pt_ctx* c) {
     if (c->copy_stream) return PT_OK;
-    CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    // highest priority: a copy, or the small kernels of a pipelined combine (pt_comm.cu), go ahead of the render stream's
+    // queued blocks whenever an SM has room
+    int prio_lo = 0, prio_hi = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CK(cudaStreamCreateWithPriority(&c->copy_stream, cudaStreamNonBlocking, prio_hi));
     CK(cudaEventCreateWithFlags(&c->ev_image, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_copied, cudaEventDisableTiming));
     return PT_OK;

@@ -18,6 +18,7 @@ int pt_fail(int code, const std::string& msg);          // records the thread-lo
 
 struct PtComm;                                           // pt_comm.cu: multi-GPU state of a context
 void pt_comm_release(struct pt_ctx* c);                  // called by pt_destroy
+int pt_comm_check(struct pt_ctx* c);                     // called by pt_synchronize: error flag of the pipelined combine
 extern "C" int pt_copy_setup(struct pt_ctx* c);          // pt_api.cu (internal, not in pt.h): creates the copy stream + events on first use
 extern "C" int pt_copy_enqueue(struct pt_ctx* c, void* host, const void* dev, size_t bytes, bool first);   // D2H on the copy stream, after ev_image
 

@@ -22,13 +22,13 @@ MODE_FAST, MODE_PARITY_REF, MODE_PARITY_WIDE, MODE_PARITY_FAST, MODE_FAST_COUNT 
 DEFAULT_BOUNCES = {LAMBERT: 2, DISNEY_UNIFORM: 5, DISNEY_IS_MIS: 2}
 
 ACC_MEAN, ACC_SUM = 0, 1
-COMBINE_SUM, COMBINE_DISJOINT, COMBINE_DISPLAY, COMBINE_ASYNC = 0, 1, 4, 8
+COMBINE_SUM, COMBINE_DISJOINT, COMBINE_DISPLAY, COMBINE_ASYNC, COMBINE_PIPELINED = 0, 1, 4, 8, 16
 COMM_ID_BYTES = 128
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 ENV_TABLE, ENV_CDF_SEARCH = 0, 1
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
            "pt_clear", "pt_readback", "pt_readback_async", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
-           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_calculate_hdr_cache_noalloc", "pt_measure_l2_read_gbs", "pt_kernel_sass_hash", "pt_comm_get_unique_id", "pt_comm_init", "pt_comm_info", "pt_comm_destroy", "pt_combine", "pt_last_error",
+           "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_calculate_hdr_cache_noalloc", "pt_measure_l2_read_gbs", "pt_kernel_sass_hash", "pt_comm_get_unique_id", "pt_comm_init", "pt_comm_info", "pt_comm_destroy", "pt_combine", "pt_combine_fence", "pt_last_error",
            "pt_build_info"]
 
 
@@ -90,6 +90,7 @@ def lib():
         "pt_comm_info": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
         "pt_comm_destroy": (C.c_int, [vp]),
         "pt_combine": (C.c_int, [vp, C.c_int, C.c_uint, vp, vp]),
+        "pt_combine_fence": (C.c_int, [vp]),
         "pt_calculate_hdr_cache": (C.c_int, [C.c_int, C.POINTER(C.c_float), C.c_int, C.c_int, C.POINTER(C.c_float)]),
         "pt_calculate_hdr_cache_noalloc": (C.c_int, [C.c_int, vp, C.c_int, C.c_int, vp, vp]),
         "pt_measure_l2_read_gbs": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
@@ -234,6 +235,10 @@ class PathTracer:
         """Collective: all ranks' framebuffers -> one image on rank 0 (pt_combine).  flags = COMBINE_SUM | COMBINE_DISJOINT
         [| COMBINE_DISPLAY], the same on every rank; out_ptr / display_ptr: host addresses on rank 0, or None."""
         _check(lib().pt_combine(self._h, flags, total_frames, out_ptr, display_ptr), "pt_combine")
+
+    def combine_fence(self):
+        """The render stream waits (on the device) for every pipelined combine issued so far, on every rank."""
+        _check(lib().pt_combine_fence(self._h), "pt_combine_fence")
 
     def combine_readback(self, kind, total_frames=0, display=False):
         """Rank 0: returns the combined float32 [H, W, 4] image (and the uint8 display image); other ranks: None."""

@@ -53,11 +53,22 @@ def test_combine_with_a_world_of_one(R):
     pt.render_spp(NF, 16)
     pt.synchronize()
     assert hf.numpy().tobytes() == ref.tobytes()
+    # PT_COMBINE_PIPELINED needs peers: with a world of one the flag means PT_COMBINE_ASYNC, and the fence has nothing to wait for
+    hf.zero_()
+    pt.clear()
+    pt.render_spp(0, NF)
+    pt.combine(R.COMBINE_DISJOINT | R.COMBINE_PIPELINED, NF, hf.data_ptr(), None)
+    pt.combine_fence()
+    pt.render_spp(NF, 16)
+    pt.synchronize()
+    assert hf.numpy().tobytes() == ref.tobytes()
     # argument checks
     with pytest.raises(R.PtError, match="total_frames"):
         pt.combine(R.COMBINE_SUM, 0)
     with pytest.raises(R.PtError, match="flags"):
         pt.combine(2, 1)
+    with pytest.raises(R.PtError, match="flags"):
+        pt.combine(32, 1)
     pt.close()
     q = R.PathTracer(8, 8, 0)
     with pytest.raises(R.PtError, match="pt_comm_init first"):
