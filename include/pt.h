@@ -174,6 +174,11 @@ int pt_readback_async(pt_ctx* ctx, float* rgba_pinned, size_t bytes);
    conversion on the device; W*H RGBA8, row 0 = TOP row (image order), alpha 255.  A quarter of pt_readback's bytes
    cross PCIe.  Synchronises. */
 int pt_readback_display(pt_ctx* ctx, unsigned char* rgba8, size_t bytes);
+/* pt_readback_display without the wait, for a display() loop (M:659-709) that draws frame k while frame k + 1 renders: the
+   display pass runs now (stream-ordered: the image as of this call) into a staging image and the copy to `rgba8_pinned`
+   (pinned host memory) rides on a second stream under the next pt_render_spp.  The buffer is valid after
+   pt_synchronize(ctx); one copy in flight per context, as for pt_readback_async.  No reference equivalent. */
+int pt_readback_display_async(pt_ctx* ctx, unsigned char* rgba8_pinned, size_t bytes);
 /* Parity hook: triangle index (into the uploaded array) of the primary hit of the LAST frame rendered, -1 = miss. */
 int pt_readback_primary_ids(pt_ctx* ctx, int* ids, size_t bytes);
 

@@ -27,7 +27,7 @@ COMM_ID_BYTES = 128
 MEGAKERNEL, WAVEFRONT, PERSISTENT = 0, 1, 2
 ENV_TABLE, ENV_CDF_SEARCH = 0, 1
 EXPORTS = ["pt_create", "pt_destroy", "pt_upload_scene", "pt_set_camera", "pt_set_region", "pt_set_band_interleave", "pt_set_tile_interleave", "pt_render_spp", "pt_render_frames",
-           "pt_clear", "pt_readback", "pt_readback_async", "pt_readback_display", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
+           "pt_clear", "pt_readback", "pt_readback_async", "pt_readback_display", "pt_readback_display_async", "pt_readback_primary_ids", "pt_enable_cost_map", "pt_readback_cost_map", "pt_framebuffer_device_ptr", "pt_stream",
            "pt_scale_framebuffer", "pt_synchronize", "pt_get_stats", "pt_reset_stats", "pt_get_ray_histogram", "pt_calculate_hdr_cache", "pt_calculate_hdr_cache_noalloc", "pt_measure_l2_read_gbs", "pt_kernel_sass_hash", "pt_comm_get_unique_id", "pt_comm_init", "pt_comm_info", "pt_comm_destroy", "pt_combine", "pt_combine_fence", "pt_last_error",
            "pt_build_info"]
 
@@ -73,6 +73,7 @@ def lib():
         "pt_readback_async": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_readback_primary_ids": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_readback_display": (C.c_int, [vp, vp, C.c_size_t]),
+        "pt_readback_display_async": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_enable_cost_map": (C.c_int, [vp, C.c_int]),
         "pt_readback_cost_map": (C.c_int, [vp, vp, C.c_size_t]),
         "pt_framebuffer_device_ptr": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
@@ -186,6 +187,10 @@ class PathTracer:
     def readback_async(self, host_ptr, nbytes):
         """pt_readback_async: snapshot now, copy on a second stream; the (pinned) buffer is valid after synchronize()."""
         _check(lib().pt_readback_async(self._h, host_ptr, nbytes), "pt_readback_async")
+
+    def readback_display_async(self, host_ptr, nbytes):
+        """pt_readback_display_async: display pass now, copy on a second stream; the (pinned) buffer is valid after synchronize()."""
+        _check(lib().pt_readback_display_async(self._h, host_ptr, nbytes), "pt_readback_display_async")
 
     def readback_display(self) -> np.ndarray:
         """pass3.fsh tone map + 8-bit conversion on the device: uint8 [H, W, 4], row 0 = top row."""

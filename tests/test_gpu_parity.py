@@ -355,6 +355,34 @@ def test_readback_async_is_a_snapshot(R):
     pt2.close(); pt.close()
 
 
+def test_readback_display_async_is_a_snapshot(R):
+    """pt_readback_display_async: the display image AS OF THE CALL, byte for byte what pt_readback_display returns, while later
+    launches (and a later synchronous display readback) go on."""
+    import torch
+    sc = small_scene("is", "10k", hdr_res=(256, 128))
+    W, H = 256, 144
+    pt = R.PathTracer(W, H, sc.variant, mode=R.MODE_FAST)
+    pt.upload_scene(sc.tris, sc.nodes, sc.hdr, sc.hdrCache); pt.set_camera(sc.eye, sc.cam)
+    want = []
+    for k in range(3):
+        pt.render_spp(k, 1)
+        want.append(pt.readback_display().copy())
+    pt.clear()
+    host = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(3)]
+    for k in range(3):                                         # the display() loop, one sample per frame, copies overlapped
+        pt.render_spp(k, 1)
+        pt.readback_display_async(host[k].data_ptr(), host[k].numel())
+    pt.render_spp(3, 29)                                       # overwrites the framebuffer while the last copy may still run
+    later = pt.readback_display()                              # the synchronous form queues behind the copy in flight
+    pt.synchronize()
+    for k in range(3):
+        assert host[k].numpy().tobytes() == want[k].tobytes(), "frame %d" % k
+    assert not (later == want[2]).all()
+    with pytest.raises(R.PtError, match="too small"):
+        pt.readback_display_async(host[0].data_ptr(), 16)
+    pt.close()
+
+
 def test_counting_build_and_cost_map(R):
     sc = small_scene("is", "10k", hdr_res=(256, 128))
     W, H, NF = 128, 72, 2
