@@ -343,7 +343,8 @@ def run_ours(args):
         dist.broadcast(idt, src=0)
         pt.comm_init(world, rank, bytes(idt.cpu().numpy().tobytes()))
         peer = pt.comm_info()["peer_memory"]
-    flush = None if args.no_l2_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    # 256 MiB > the 126 MB L2, written as 8-byte words (torch's one-byte fill_ runs at 3.7 TB/s, this at 6.8: tools/fill_probe.py)
+    flush = None if args.no_l2_flush else torch.empty((256 << 20) // 8, dtype=torch.int64, device="cuda")
     tile, samp = D.TilePlan(W, H, world, rank), D.SamplePlan(world, rank)
     spp = args.spp
     kind = R.COMBINE_DISJOINT if args.split == "tile" else R.COMBINE_SUM
@@ -386,7 +387,7 @@ def run_ours(args):
     for k in range(args.steps):
         if flush is not None:
             with torch.cuda.stream(stream):
-                flush.fill_(k & 0xff)                 # 256 MiB > 126 MB L2, outside the per-step events
+                flush.fill_(k)                 # 256 MiB > 126 MB L2, outside the per-step events
         ev[k][0].record(stream)
         render_step(frame); frame += spp
         ev[k][1].record(stream)
