@@ -8,9 +8,12 @@ cudaError_t launch_fast(const RenderParams& p, int variant, bool count, cudaStre
     if (count) return launch_render<CfgFastCount>(p, variant, stream);   // same arithmetic + traversal work counters
     return launch_render<CfgFast>(p, variant, stream);
 }
+cudaError_t launch_persistent_fast_v2(const RenderParams& p, int grid, cudaStream_t stream);   // pt_kernels_fast_v2.cu (-ftz=true)
 cudaError_t launch_persistent_fast(const RenderParams& p, int variant, bool count, int grid, cudaStream_t stream) {
     if (count) return launch_persistent<CfgFastCount>(p, variant, grid, stream);
-    return launch_persistent<CfgFast>(p, variant, grid, stream);
+    if (variant == 0) return launch_persistent_variant<CfgFast, 0>(p, grid, stream);
+    if (variant == 1) return launch_persistent_variant<CfgFast, 1>(p, grid, stream);
+    return launch_persistent_fast_v2(p, grid, stream);    // the metric kernel lives in its own translation unit
 }
 // PT_ENV_CDF_SEARCH: variant 2 on the persistent pipeline only
 cudaError_t launch_persistent_fast_cdf(const RenderParams& p, int grid, cudaStream_t stream) { return launch_persistent_variant<CfgFastCdf, 2>(p, grid, stream); }
